@@ -1,0 +1,127 @@
+/* lmc_b200.h -- C ABI of the B200-native Langevin sampler hot path.
+ *
+ * The reference (192459/lmc-atomi) has no FFI: its boundary is the Python call
+ * surface of the sampler classes and of algs.py.  Each entry point below replaces
+ * the per-iteration Python loop named beside it; the Python side binds them with
+ * ctypes (lmc_atomi_b200/_lib.py, stub shown in INTEGRATION.md).
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error; lmc_last_error() then
+ *     returns a thread-local description;
+ *   - every pointer named d_* is a DEVICE pointer owned by the caller (e.g. a
+ *     torch tensor's data_ptr()); the library never allocates or frees user-visible
+ *     memory, scratch comes from the caller-supplied workspace;
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it
+ *     unless stated otherwise;
+ *   - dtype: LMC_F32 or LMC_F64 selects the arithmetic type of the state, noise
+ *     and trajectory buffers.
+ */
+#ifndef LMC_B200_H
+#define LMC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LMC_MAX_COMP 8
+#define LMC_F32 0
+#define LMC_F64 1
+
+const char* lmc_last_error(void);
+int lmc_version(void);
+/* number of SMs / name of the current device; <0 when no CUDA device */
+int lmc_device_sm_count(void);
+
+/* ------------------------------------------------------------------ mixtures */
+enum lmc_target_kind {
+  LMC_TARGET_GAUSS = 0,    /* lmc.py:39-78        Gaussian mixture                    */
+  LMC_TARGET_LAPLACE = 1,  /* lmc_laplace.py:43-95 Moreau-smoothed Laplacian mixture  */
+  LMC_TARGET_GAUSS_L1 = 2  /* prox_lmc.py:42-95    Gaussian mixture x Laplacian prior */
+};
+
+enum lmc_alg {
+  LMC_ULA = 0,     /* lmc.py:94-104, lmc_laplace.py:110-123 */
+  LMC_MALA = 1,    /* lmc.py:108-131, lmc_laplace.py:127-151 */
+  LMC_PULA = 2,    /* lmc.py:135-148, lmc_laplace.py:155-170 */
+  LMC_IHPULA = 3,  /* lmc.py:152-169, lmc_laplace.py:174-193 */
+  LMC_MLA = 4,     /* lmc.py:173-190, lmc_laplace.py:197-216 */
+  LMC_PGLD = 5,    /* prox_lmc.py:99-110  */
+  LMC_MYULA = 6,   /* prox_lmc.py:114-130 */
+  LMC_MYMALA = 7,  /* prox_lmc.py:134-158 */
+  LMC_PPULA = 8,   /* prox_lmc.py:162-188 */
+  LMC_FBULA = 9,   /* prox_lmc.py:192-208 */
+  LMC_LBMUMLA = 10 /* prox_lmc.py:212-255 */
+};
+
+/* Target description.  The host fills the per-component constants with the same
+ * numpy calls the reference uses (np.linalg.inv / det), so they are bit-identical. */
+typedef struct lmc_mix_target {
+  int32_t kind;                    /* enum lmc_target_kind */
+  int32_t n;                       /* components, 1..LMC_MAX_COMP */
+  double mu[LMC_MAX_COMP][2];      /* component locations */
+  double prec[LMC_MAX_COMP][4];    /* Sigma_i^-1 row-major (GAUSS, GAUSS_L1) */
+  double norm[LMC_MAX_COMP];       /* sqrt((2 pi)^2 |det Sigma_i|) (GAUSS, GAUSS_L1) */
+  double omega[LMC_MAX_COMP];      /* mixture weights */
+  double alpha[LMC_MAX_COMP];      /* Laplacian scales (LAPLACE) */
+  double lamda;                    /* Moreau smoothing (LAPLACE, GAUSS_L1) */
+  double prior_alpha;              /* l1 prior scale (GAUSS_L1) */
+  double prior_mu[2];              /* l1 prior location, used by the MH ratio only */
+} lmc_mix_target;
+
+typedef struct lmc_mix_step {
+  int32_t alg;        /* enum lmc_alg */
+  int32_t t;          /* PPULA inner dual iterations (prox_lmc.py:165) */
+  double gamma;       /* step size */
+  double M[4];        /* PULA/PPULA preconditioner, row-major */
+  double sqrtM[4];    /* scipy.linalg.sqrtm(M), host-computed */
+  double Q[4];        /* PPULA metric */
+  double Qinv[4];     /* np.linalg.inv(Q) */
+  double eta;         /* PPULA dual step rho - eps (prox_lmc.py:166-168) */
+  double beta[2];     /* MLA / LBMUMLA mirror parameter */
+  double sigma[2];    /* LBMUMLA: the vector the reference passes in the beta slot
+                         of grad_BM_env (prox_lmc.py:251) */
+  double hess_shift;  /* IHPULA eigen-shift: 0.05 (lmc.py:162) / 0.02 (lmc_laplace.py:186) */
+} lmc_mix_step;
+
+/* Buffers of one run of C chains x K steps.  NULL = not requested. */
+typedef struct lmc_mix_io {
+  void* d_theta;             /* (C,2) in/out: start state (ignored when init_from_rng) -> final state */
+  const void* d_noise;       /* (C,K,2) validation mode: host-supplied N(0,1) draws; NULL = Philox */
+  const void* d_uniforms;    /* (C,K) validation mode, adjusted samplers */
+  void* d_traj;              /* (C,K,2) state after every step */
+  uint8_t* d_accept;         /* (C,K) accept flags (adjusted samplers) */
+  uint32_t* d_naccept;       /* (C,) accepted proposals per chain */
+  double* d_moments;         /* (6,) count, S(t0), S(t1), S(t0^2), S(t0 t1), S(t1^2) over emitted samples */
+  unsigned long long* d_hist;/* (hist_bins,hist_bins) counts, [x-bin][y-bin], ADDED to */
+  void* d_workspace;         /* >= lmc_mix_workspace_bytes(C) */
+  size_t workspace_bytes;
+  int32_t init_from_rng;     /* 1: theta0 ~ N(0,I) from the chain's Philox stream */
+  int32_t hist_bins;         /* e.g. 100 (lmc.py:295) */
+  double hist_lo, hist_hi;   /* square range, e.g. [-5,5] (lmc.py:199-200) */
+  int64_t hist_every;        /* >0: bin every hist_every-th emitted step; 0: final state only */
+  int64_t burnin;            /* steps excluded from moments/histogram */
+} lmc_mix_io;
+
+size_t lmc_mix_workspace_bytes(int64_t C);
+
+/* Runs C independent chains for K steps in ONE persistent launch (+ a tiny
+ * fixed-order reduction of the moment partials).  Chain c uses Philox4x32-10 with
+ * key = seed and counter words (step, stream, c + chain_offset), so results do not
+ * depend on how chains are sharded over GPUs. */
+int lmc_mix_run(const lmc_mix_target* target, const lmc_mix_step* step, int dtype,
+                int64_t C, int64_t K, uint64_t seed, uint64_t chain_offset,
+                const lmc_mix_io* io, void* stream);
+
+/* Test hook: the N(0,1) pairs (and uniforms) the production path draws:
+ * d_normals (C,K,2), d_uniforms (C,K) or NULL, d_theta0 (C,2) or NULL. */
+int lmc_mix_philox_draws(int dtype, int adjusted, int64_t C, int64_t K, uint64_t seed,
+                         uint64_t chain_offset, void* d_normals, void* d_uniforms,
+                         void* d_theta0, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LMC_B200_H */

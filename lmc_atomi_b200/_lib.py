@@ -1,0 +1,101 @@
+"""ctypes binding of the C-ABI declared in include/lmc_b200.h.
+
+The shared library is built in-tree by ``lmc_atomi_b200/build.py`` (nvcc, sm_100a).
+There is deliberately no fallback: if the library is missing, cannot be loaded, or a
+call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "_lmc_b200.so")
+
+MAX_COMP = 8
+F32, F64 = 0, 1
+
+TARGET_GAUSS, TARGET_LAPLACE, TARGET_GAUSS_L1 = 0, 1, 2
+ALGS = {"ula": 0, "mala": 1, "pula": 2, "ihpula": 3, "mla": 4, "pgld": 5, "myula": 6,
+        "mymala": 7, "ppula": 8, "fbula": 9, "lbmumla": 10}
+
+
+class LmcError(RuntimeError):
+    pass
+
+
+class MixTarget(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("n", C.c_int32),
+                ("mu", (C.c_double * 2) * MAX_COMP),
+                ("prec", (C.c_double * 4) * MAX_COMP),
+                ("norm", C.c_double * MAX_COMP),
+                ("omega", C.c_double * MAX_COMP),
+                ("alpha", C.c_double * MAX_COMP),
+                ("lamda", C.c_double),
+                ("prior_alpha", C.c_double),
+                ("prior_mu", C.c_double * 2)]
+
+
+class MixStep(C.Structure):
+    _fields_ = [("alg", C.c_int32), ("t", C.c_int32), ("gamma", C.c_double),
+                ("M", C.c_double * 4), ("sqrtM", C.c_double * 4),
+                ("Q", C.c_double * 4), ("Qinv", C.c_double * 4),
+                ("eta", C.c_double),
+                ("beta", C.c_double * 2), ("sigma", C.c_double * 2),
+                ("hess_shift", C.c_double)]
+
+
+class MixIo(C.Structure):
+    _fields_ = [("d_theta", C.c_void_p), ("d_noise", C.c_void_p), ("d_uniforms", C.c_void_p),
+                ("d_traj", C.c_void_p), ("d_accept", C.c_void_p), ("d_naccept", C.c_void_p),
+                ("d_moments", C.c_void_p), ("d_hist", C.c_void_p),
+                ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+                ("init_from_rng", C.c_int32), ("hist_bins", C.c_int32),
+                ("hist_lo", C.c_double), ("hist_hi", C.c_double),
+                ("hist_every", C.c_int64), ("burnin", C.c_int64)]
+
+
+# name -> (restype, argtypes); must list every symbol include/lmc_b200.h declares
+SIGNATURES = {
+    "lmc_last_error": (C.c_char_p, []),
+    "lmc_version": (C.c_int, []),
+    "lmc_device_sm_count": (C.c_int, []),
+    "lmc_mix_workspace_bytes": (C.c_size_t, [C.c_int64]),
+    "lmc_mix_run": (C.c_int, [C.POINTER(MixTarget), C.POINTER(MixStep), C.c_int, C.c_int64,
+                              C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(MixIo), C.c_void_p]),
+    "lmc_mix_philox_draws": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_uint64,
+                                       C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the CUDA library (once).  Raises LmcError when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise LmcError(
+            f"{LIB_PATH} not found: build it with `python -m lmc_atomi_b200.build` "
+            "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().lmc_last_error().decode("utf-8", "replace")
+        raise LmcError(f"{what} failed ({rc}): {msg}")
+
+
+def require_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        raise LmcError("lmc_atomi_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    return torch

@@ -1,0 +1,681 @@
+// Persistent register-resident Langevin chains on 2-D mixture targets.
+//
+// One thread = one chain; all K steps of the chain run inside ONE launch with the
+// state (theta, Philox counter, running moments) held in registers.  A warp grabs
+// 32 consecutive chains from a global queue (dynamic, warp-granular scheduling, so
+// the 148 SMs stay balanced for any C), steps them K times and writes the final
+// state, accept count and its moment partials.  Steady-state HBM traffic is zero:
+// the kernel is bound by FP32/INT32 issue and the MUFU pipe (kernel M1).
+//
+// Reference loops replaced (file:line under /root/reference):
+//   lmc.py:94-190, lmc_laplace.py:110-216, prox_lmc.py:99-255
+// The target is evaluated in the log2 domain with a max-shift (log-sum-exp), which
+// is algebraically identical to the reference's plain ratio -grad p / p
+// (lmc.py:60-61) but cannot underflow in fp32.
+#include "lmc_common.cuh"
+
+namespace {
+
+constexpr int NMAX = LMC_MAX_COMP;
+constexpr int BLOCK = 256;
+
+template <typename real>
+struct MixP {
+  int n, t;
+  // components
+  real mu0[NMAX], mu1[NMAX];
+  real p00[NMAX], p01[NMAX], p10[NMAX], p11[NMAX];  // Sigma^-1 (Gaussian kinds)
+  real lc[NMAX];    // log2 of the component's constant factor (omega_i / norm_i or omega_i (alpha_i/2)^2)
+  real al[NMAX];    // Laplacian scale alpha_i
+  real thr[NMAX];   // lamda * alpha_i
+  real lamda, inv_lamda;
+  // l1 prior (GAUSS_L1)
+  real pr_alpha, pr_thr, pr_mu0, pr_mu1;
+  // step
+  real gamma, s2g, inv4g;
+  real m00, m01, m10, m11;      // M
+  real s00, s01, s10, s11;      // sqrtm(M)
+  real q00, q01, q10, q11;      // Q
+  real qi00, qi01, qi10, qi11;  // Q^-1
+  real eta, inv_eta, pp_thr;    // PPULA dual step, 1/eta, lamda/eta
+  real b0, b1, sg0, sg1;        // beta, sigma
+  real hshift;
+};
+
+struct MixIo {
+  void* theta;
+  const void* noise;
+  const void* unif;
+  void* traj;
+  uint8_t* accept;
+  uint32_t* naccept;
+  unsigned long long* hist;
+  unsigned int* queue;   // workspace: work-item counter
+  double* partial;       // workspace: (n_items, 6) moment partials
+  long long C, K, burnin, hist_every;
+  unsigned long long chain_offset;
+  uint2 key;
+  int init_from_rng, hist_bins;
+  double hist_lo, hist_scale;  // bin = floor((x - lo) * scale)
+  int n_items;
+};
+
+template <typename real>
+struct Eval {
+  real g0, g1;       // grad U
+  real logp2;        // log2 of the (smoothed) mixture density
+  real h00, h01, h11;  // Hessian of U (only when requested)
+};
+
+constexpr float LOG2E_F = 1.4426950408889634f;
+
+// ----------------------------------------------------------------------------------
+// Gaussian mixture: lmc.py:39-75.  a_i = log2(omega_i N_i(theta)); softmax weights
+// w_i = 2^(a_i - max a); grad U = sum w_i P_i (theta - mu_i) / sum w_i.
+template <typename real, int NC, bool HESS>
+__device__ __forceinline__ void eval_gauss(const MixP<real>& P, real t0, real t1, Eval<real>& e) {
+  using M = Math<real>;
+  const int n = NC > 0 ? NC : P.n;
+  real a[NMAX], v0[NMAX], v1[NMAX];
+  real amax = real(-1e30);
+#pragma unroll
+  for (int i = 0; i < NMAX; ++i) {
+    if (i < n) {
+      real d0 = t0 - P.mu0[i], d1 = t1 - P.mu1[i];
+      v0[i] = M::fma(P.p00[i], d0, P.p01[i] * d1);
+      v1[i] = M::fma(P.p10[i], d0, P.p11[i] * d1);
+      real fac = M::fma(d0, v0[i], d1 * v1[i]);
+      a[i] = M::fma(fac, real(-0.5 * 1.4426950408889634), P.lc[i]);
+      amax = M::max(amax, a[i]);
+    }
+  }
+  real S = 0, gp0 = 0, gp1 = 0, hp00 = 0, hp01 = 0, hp11 = 0;
+#pragma unroll
+  for (int i = 0; i < NMAX; ++i) {
+    if (i < n) {
+      real w = M::exp2(a[i] - amax);
+      S += w;
+      gp0 = M::fma(w, v0[i], gp0);  // note: this is -grad p (sign folded)
+      gp1 = M::fma(w, v1[i], gp1);
+      if (HESS) {  // lmc.py:63-65: N_i (P d d^T P - P)
+        hp00 = M::fma(w, M::fma(v0[i], v0[i], -P.p00[i]), hp00);
+        hp01 = M::fma(w, M::fma(v0[i], v1[i], -real(0.5) * (P.p01[i] + P.p10[i])), hp01);
+        hp11 = M::fma(w, M::fma(v1[i], v1[i], -P.p11[i]), hp11);
+      }
+    }
+  }
+  real rS = M::rcp(S);
+  e.g0 = gp0 * rS;
+  e.g1 = gp1 * rS;
+  e.logp2 = amax + M::log2(S);
+  if (HESS) {  // lmc.py:71-75: grad p grad p^T / p^2 - hess p / p
+    e.h00 = M::fma(e.g0, e.g0, -hp00 * rS);
+    e.h01 = M::fma(e.g0, e.g1, -hp01 * rS);
+    e.h11 = M::fma(e.g1, e.g1, -hp11 * rS);
+  }
+}
+
+// Moreau-smoothed Laplacian mixture: lmc_laplace.py:43-92.
+template <typename real, int NC, bool HESS>
+__device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real t1, Eval<real>& e) {
+  using M = Math<real>;
+  const int n = NC > 0 ? NC : P.n;
+  real a[NMAX], v0[NMAX], v1[NMAX];
+  real amax = real(-1e30);
+  const real l2e = real(1.4426950408889634);
+#pragma unroll
+  for (int i = 0; i < NMAX; ++i) {
+    if (i < n) {
+      real d0 = t0 - P.mu0[i], d1 = t1 - P.mu1[i];
+      real s0 = lmc_soft(d0, P.thr[i]), s1 = lmc_soft(d1, P.thr[i]);  // prox - mu  (lmc_laplace.py:53-54)
+      real r0 = d0 - s0, r1 = d1 - s1;                               // theta - prox
+      // Moreau envelope (lmc_laplace.py:56-58)
+      real env = M::fma(P.al[i], M::abs(s0) + M::abs(s1),
+                        M::fma(r0, r0, r1 * r1) * (real(0.5) * P.inv_lamda));
+      a[i] = M::fma(env, -l2e, P.lc[i]);
+      v0[i] = r0 * P.inv_lamda;  // (theta - prox)/lamda = -grad of the component / pdf
+      v1[i] = r1 * P.inv_lamda;
+      amax = M::max(amax, a[i]);
+    }
+  }
+  real S = 0, gp0 = 0, gp1 = 0, hp00 = 0, hp01 = 0, hp11 = 0;
+  real l1 = M::abs(t0) + M::abs(t1);
+#pragma unroll
+  for (int i = 0; i < NMAX; ++i) {
+    if (i < n) {
+      real w = M::exp2(a[i] - amax);
+      S += w;
+      gp0 = M::fma(w, v0[i], gp0);
+      gp1 = M::fma(w, v1[i], gp1);
+      if (HESS) {
+        // lmc_laplace.py:80-82 (sic): weight (alpha/2)^2 exp(-alpha ||theta||_1), no mu,
+        // unsmoothed exponent; matrix (-I + g g^T).
+        real wq = M::exp2(M::fma(P.al[i] * l1, -l2e, P.lc[i]) - amax);
+        hp00 = M::fma(wq, M::fma(v0[i], v0[i], real(-1)), hp00);
+        hp01 = M::fma(wq, v0[i] * v1[i], hp01);
+        hp11 = M::fma(wq, M::fma(v1[i], v1[i], real(-1)), hp11);
+      }
+    }
+  }
+  real rS = M::rcp(S);
+  e.g0 = gp0 * rS;
+  e.g1 = gp1 * rS;
+  e.logp2 = amax + M::log2(S);
+  if (HESS) {
+    e.h00 = M::fma(e.g0, e.g0, -hp00 * rS);
+    e.h01 = M::fma(e.g0, e.g1, -hp01 * rS);
+    e.h11 = M::fma(e.g1, e.g1, -hp11 * rS);
+  }
+}
+
+template <typename real, int TARGET, int NC, bool HESS>
+__device__ __forceinline__ void eval_target(const MixP<real>& P, real t0, real t1, Eval<real>& e) {
+  if (TARGET == LMC_TARGET_LAPLACE) eval_laplace<real, NC, HESS>(P, t0, t1, e);
+  else eval_gauss<real, NC, HESS>(P, t0, t1, e);
+}
+
+// closed-form inverse and principal square root of a symmetric positive definite 2x2
+template <typename real>
+__device__ __forceinline__ void spd_inv_sqrt(real a, real b, real d, real& i00, real& i01, real& i11,
+                                             real& r00, real& r01, real& r11) {
+  using M = Math<real>;
+  real det = M::fma(a, d, -b * b);
+  real rdet = real(1) / det;
+  i00 = d * rdet; i01 = -b * rdet; i11 = a * rdet;          // M = H^-1
+  real sdet = M::sqrt(M::fma(i00, i11, -i01 * i01));        // sqrt(det M)
+  real tr = i00 + i11;
+  real rs = real(1) / M::sqrt(tr + real(2) * sdet);
+  r00 = (i00 + sdet) * rs; r01 = i01 * rs; r11 = (i11 + sdet) * rs;  // sqrtm(M)
+}
+
+template <int ALG> struct AlgTraits {
+  static constexpr bool adjusted = (ALG == LMC_MALA || ALG == LMC_MYMALA);
+  static constexpr bool hess = (ALG == LMC_IHPULA || ALG == LMC_FBULA);
+};
+
+// mean of the Langevin proposal: "gd_update" (lmc.py:77-78) plus, for MYMALA/MYULA,
+// the Moreau-Yosida drift "prox_update" (prox_lmc.py:114-118)
+template <typename real, int ALG>
+__device__ __forceinline__ void drift_centre(const MixP<real>& P, real t0, real t1, const Eval<real>& e,
+                                             real& c0, real& c1) {
+  using M = Math<real>;
+  c0 = M::fma(-P.gamma, e.g0, t0);
+  c1 = M::fma(-P.gamma, e.g1, t1);
+  if (ALG == LMC_MYULA || ALG == LMC_MYMALA) {
+    real y0 = (t0 - lmc_soft(t0, P.pr_thr)) * P.inv_lamda;
+    real y1 = (t1 - lmc_soft(t1, P.pr_thr)) * P.inv_lamda;
+    c0 = M::fma(-P.gamma, y0, c0);
+    c1 = M::fma(-P.gamma, y1, c1);
+  }
+}
+
+// One transition of an unadjusted sampler.
+template <typename real, int TARGET, int ALG, int NC>
+__device__ __forceinline__ void step_unadjusted(const MixP<real>& P, real& t0, real& t1, real x0, real x1) {
+  using M = Math<real>;
+  Eval<real> e;
+  if (ALG == LMC_PGLD) {  // prox_lmc.py:106
+    t0 = lmc_soft(t0, P.pr_thr);
+    t1 = lmc_soft(t1, P.pr_thr);
+  }
+  eval_target<real, TARGET, NC, AlgTraits<ALG>::hess>(P, t0, t1, e);
+  if (ALG == LMC_ULA || ALG == LMC_PGLD || ALG == LMC_MYULA) {
+    real c0, c1;
+    drift_centre<real, ALG>(P, t0, t1, e, c0, c1);
+    t0 = M::fma(P.s2g, x0, c0);
+    t1 = M::fma(P.s2g, x1, c1);
+  } else if (ALG == LMC_PULA || ALG == LMC_PPULA) {
+    real n0 = M::fma(P.m00, e.g0, P.m01 * e.g1), n1 = M::fma(P.m10, e.g0, P.m11 * e.g1);
+    real z0 = M::fma(P.s00, x0, P.s01 * x1), z1 = M::fma(P.s10, x0, P.s11 * x1);
+    real c0 = M::fma(-P.gamma, n0, t0), c1 = M::fma(-P.gamma, n1, t1);
+    if (ALG == LMC_PPULA) {
+      // prox_lmc.py:165-176: dual forward-backward iterations for prox in the Q metric,
+      // called with threshold lamda (sic, not lamda*alpha); returns the last primal u.
+      real w0 = 0, w1 = 0, u0 = t0, u1 = t1;
+      for (int it = 0; it < P.t; ++it) {
+        u0 = t0 - M::fma(P.q00, w0, P.q01 * w1);
+        u1 = t1 - M::fma(P.q10, w0, P.q11 * w1);
+        real y0 = M::fma(w0, P.inv_eta, u0), y1 = M::fma(w1, P.inv_eta, u1);
+        w0 = M::fma(P.eta, u0, w0) - P.eta * lmc_soft(y0, P.pp_thr);
+        w1 = M::fma(P.eta, u1, w1) - P.eta * lmc_soft(y1, P.pp_thr);
+      }
+      real r0 = t0 - u0, r1 = t1 - u1;
+      real k0 = M::fma(P.qi00, r0, P.qi01 * r1) * P.inv_lamda;
+      real k1 = M::fma(P.qi10, r0, P.qi11 * r1) * P.inv_lamda;
+      c0 = M::fma(-P.gamma, k0, c0);
+      c1 = M::fma(-P.gamma, k1, c1);
+    }
+    t0 = M::fma(P.s2g, z0, c0);
+    t1 = M::fma(P.s2g, z1, c1);
+  } else if (ALG == LMC_IHPULA) {
+    // lmc.py:159-166: M = (H + (|lambda_min| + shift) I)^-1 (n>1) or H^-1 (n==1)
+    real a = e.h00, b = e.h01, d = e.h11;
+    if (P.n > 1) {
+      real hm = real(0.5) * (a + d), hd = real(0.5) * (a - d);
+      real emin = hm - M::sqrt(M::fma(hd, hd, b * b));
+      real sh = M::abs(emin) + P.hshift;
+      a += sh; d += sh;
+    }
+    real i00, i01, i11, r00, r01, r11;
+    spd_inv_sqrt(a, b, d, i00, i01, i11, r00, r01, r11);
+    real n0 = M::fma(i00, e.g0, i01 * e.g1), n1 = M::fma(i01, e.g0, i11 * e.g1);
+    real z0 = M::fma(r00, x0, r01 * x1), z1 = M::fma(r01, x0, r11 * x1);
+    t0 = M::fma(P.s2g, z0, M::fma(-P.gamma, n0, t0));
+    t1 = M::fma(P.s2g, z1, M::fma(-P.gamma, n1, t1));
+  } else if (ALG == LMC_MLA || ALG == LMC_LBMUMLA) {
+    // lmc.py:186-187 / prox_lmc.py:251-252: mirror map grad = asinh(theta/beta)
+    real q0 = M::fma(t0, t0, P.b0 * P.b0), q1 = M::fma(t1, t1, P.b1 * P.b1);
+    real e0 = M::asinh(t0 / P.b0) - P.gamma * e.g0;
+    real e1 = M::asinh(t1 / P.b1) - P.gamma * e.g1;
+    if (ALG == LMC_LBMUMLA) {
+      // prox_lmc.py:218-242 with beta := sigma (the reference passes sigma there)
+      real thr = P.pr_thr;
+      real sh = M::sinh(thr);
+      {
+        real as = M::asinh(t0 / P.sg0);
+        real lo = P.sg0 * M::sinh(as - thr), hi = P.sg0 * M::sinh(as + thr);
+        real rt = M::sqrt(M::fma(t0, t0, P.sg0 * P.sg0));
+        real p = (t0 > P.sg0 * sh) ? lo : (rt - P.sg0);
+        p = (t0 < -P.sg0 * sh) ? hi : p;
+        e0 -= P.gamma * (P.inv_lamda / rt * (t0 - p));
+      }
+      {
+        real as = M::asinh(t1 / P.sg1);
+        real lo = P.sg1 * M::sinh(as - thr), hi = P.sg1 * M::sinh(as + thr);
+        real rt = M::sqrt(M::fma(t1, t1, P.sg1 * P.sg1));
+        real p = (t1 > P.sg1 * sh) ? lo : (rt - P.sg1);
+        p = (t1 < -P.sg1 * sh) ? hi : p;
+        e1 -= P.gamma * (P.inv_lamda / rt * (t1 - p));
+      }
+    }
+    e0 = M::fma(P.s2g * M::rsqrt(M::sqrt(q0)), x0, e0);
+    e1 = M::fma(P.s2g * M::rsqrt(M::sqrt(q1)), x1, e1);
+    t0 = P.b0 * M::sinh(e0);
+    t1 = P.b1 * M::sinh(e1);
+  } else if (ALG == LMC_FBULA) {
+    // prox_lmc.py:192-196: (I - lamda H)(theta - soft(theta - lamda grad U, lamda alpha))/lamda
+    real f0 = M::fma(-P.lamda, e.g0, t0), f1 = M::fma(-P.lamda, e.g1, t1);
+    real r0 = t0 - lmc_soft(f0, P.pr_thr), r1 = t1 - lmc_soft(f1, P.pr_thr);
+    real a = real(1) - P.lamda * e.h00, b = -P.lamda * e.h01, d = real(1) - P.lamda * e.h11;
+    real k0 = M::fma(a, r0, b * r1) * P.inv_lamda, k1 = M::fma(b, r0, d * r1) * P.inv_lamda;
+    t0 = M::fma(P.s2g, x0, M::fma(-P.gamma, k0, t0));
+    t1 = M::fma(P.s2g, x1, M::fma(-P.gamma, k1, t1));
+  }
+}
+
+// log2 of the density entering the MH ratio (lmc.py:113, lmc_laplace.py:131, prox_lmc.py:139-140)
+template <typename real, int ALG>
+__device__ __forceinline__ real mh_logdens2(const MixP<real>& P, real t0, real t1, const Eval<real>& e) {
+  using M = Math<real>;
+  real l = e.logp2;
+  if (ALG == LMC_MYMALA)
+    l -= real(1.4426950408889634) * P.pr_alpha * (M::abs(t0 - P.pr_mu0) + M::abs(t1 - P.pr_mu1));
+  return l;
+}
+
+template <typename real, int TARGET, int ALG, int NC>
+__global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant__ MixP<real> P,
+                                                          const __grid_constant__ MixIo io) {
+  using M = Math<real>;
+  constexpr bool ADJ = AlgTraits<ALG>::adjusted;
+  const int lane = threadIdx.x & 31;
+  real* theta = (real*)io.theta;
+  const real* noise = (const real*)io.noise;
+  const real* unif = (const real*)io.unif;
+  real* traj = (real*)io.traj;
+  const long long K = io.K;
+
+  for (;;) {
+    unsigned int item = 0;
+    if (lane == 0) item = atomicAdd(io.queue, 1u);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= (unsigned)io.n_items) break;
+    const long long c = (long long)item * 32 + lane;
+    const bool live = c < io.C;
+    const unsigned long long gc = io.chain_offset + (unsigned long long)(live ? c : 0);
+    const uint32_t c_lo = (uint32_t)gc, c_hi = (uint32_t)(gc >> 32);
+
+    real t0 = 0, t1 = 0;
+    if (io.init_from_rng) {
+      uint4 r = lmc_philox4x32_10(make_uint4(0u, LMC_STREAM_INIT, c_lo, c_hi), io.key);
+      M::normals(r.x, r.y, t0, t1);
+    } else if (live) {
+      t0 = theta[2 * c];
+      t1 = theta[2 * c + 1];
+    }
+
+    // state of the MH chain: value of the target and the proposal centre at theta
+    Eval<real> cur;
+    real cc0 = 0, cc1 = 0, clog = 0;
+    if (ADJ) {
+      eval_target<real, TARGET, NC, false>(P, t0, t1, cur);
+      drift_centre<real, ALG>(P, t0, t1, cur, cc0, cc1);
+      clog = mh_logdens2<real, ALG>(P, t0, t1, cur);
+    }
+
+    double m_n = 0, m_s0 = 0, m_s1 = 0, m_s00 = 0, m_s01 = 0, m_s11 = 0;
+    real b_n = 0, b_s0 = 0, b_s1 = 0, b_s00 = 0, b_s01 = 0, b_s11 = 0;  // 32-step blocks
+    uint32_t nacc = 0;
+    uint4 rnd = make_uint4(0, 0, 0, 0);
+
+    for (long long k = 0; k < K; ++k) {
+      // ---- noise: validation mode reads the host-supplied draws, production mode uses
+      // Philox: one block per step for adjusted samplers (2 normals + 1 uniform), one
+      // block per TWO steps otherwise.
+      real x0, x1, u = 0;
+      if (noise != nullptr) {
+        x0 = live ? noise[(c * K + k) * 2] : real(0);
+        x1 = live ? noise[(c * K + k) * 2 + 1] : real(0);
+        if (ADJ) u = live ? unif[c * K + k] : real(0);
+      } else if (ADJ) {
+        rnd = lmc_philox4x32_10(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), io.key);
+        M::normals(rnd.x, rnd.y, x0, x1);
+        u = M::uniform(rnd.z);
+      } else {
+        if ((k & 1) == 0) {
+          long long kb = k >> 1;
+          rnd = lmc_philox4x32_10(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), io.key);
+          M::normals(rnd.x, rnd.y, x0, x1);
+        } else {
+          M::normals(rnd.z, rnd.w, x0, x1);
+        }
+      }
+
+      bool emitted = true;
+      if (!ADJ) {
+        step_unadjusted<real, TARGET, ALG, NC>(P, t0, t1, x0, x1);
+      } else {
+        // lmc.py:124-130: propose, MH ratio p(new) q(old|new) / (p(old) q(new|old)),
+        // accept iff u <= min(1, ratio); a NaN ratio accepts (Python's min(1, nan) == 1).
+        real n0 = M::fma(P.s2g, x0, cc0), n1 = M::fma(P.s2g, x1, cc1);
+        Eval<real> prop;
+        eval_target<real, TARGET, NC, false>(P, n0, n1, prop);
+        real pc0, pc1;
+        drift_centre<real, ALG>(P, n0, n1, prop, pc0, pc1);
+        real plog = mh_logdens2<real, ALG>(P, n0, n1, prop);
+        real f0 = t0 - pc0, f1 = t1 - pc1;   // old | new
+        real r0 = n0 - cc0, r1 = n1 - cc1;   // new | old
+        real lq = (M::fma(r0, r0, r1 * r1) - M::fma(f0, f0, f1 * f1)) * P.inv4g;  // natural log
+        real lr2 = (plog - clog) + real(1.4426950408889634) * lq;
+        real ratio = M::exp2(lr2);
+        emitted = !(u > M::min(real(1), ratio));
+        if (emitted) {
+          t0 = n0; t1 = n1; cc0 = pc0; cc1 = pc1; clog = plog;
+          ++nacc;
+        }
+        if (io.accept != nullptr && live) io.accept[c * K + k] = emitted ? 1 : 0;
+      }
+
+      if (traj != nullptr && live) {
+        traj[(c * K + k) * 2] = t0;
+        traj[(c * K + k) * 2 + 1] = t1;
+      }
+      // ---- running statistics over the emitted samples
+      if (k >= io.burnin) {
+        real f = emitted ? real(1) : real(0);
+        b_n += f;
+        b_s0 = M::fma(f, t0, b_s0);
+        b_s1 = M::fma(f, t1, b_s1);
+        b_s00 = M::fma(f * t0, t0, b_s00);
+        b_s01 = M::fma(f * t0, t1, b_s01);
+        b_s11 = M::fma(f * t1, t1, b_s11);
+        if ((k & 31) == 31) {
+          m_n += b_n; m_s0 += b_s0; m_s1 += b_s1; m_s00 += b_s00; m_s01 += b_s01; m_s11 += b_s11;
+          b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = 0;
+        }
+        if (io.hist != nullptr && io.hist_every > 0 && emitted && live && ((k + 1) % io.hist_every == 0)) {
+          int ix = (int)floor(((double)t0 - io.hist_lo) * io.hist_scale);
+          int iy = (int)floor(((double)t1 - io.hist_lo) * io.hist_scale);
+          if (ix >= 0 && ix < io.hist_bins && iy >= 0 && iy < io.hist_bins)
+            atomicAdd(&io.hist[ix * io.hist_bins + iy], 1ull);
+        }
+      }
+    }
+    m_n += b_n; m_s0 += b_s0; m_s1 += b_s1; m_s00 += b_s00; m_s01 += b_s01; m_s11 += b_s11;
+
+    if (live) {
+      theta[2 * c] = t0;
+      theta[2 * c + 1] = t1;
+      if (io.naccept != nullptr) io.naccept[c] = ADJ ? nacc : (uint32_t)K;
+      if (io.hist != nullptr && io.hist_every == 0) {
+        int ix = (int)floor(((double)t0 - io.hist_lo) * io.hist_scale);
+        int iy = (int)floor(((double)t1 - io.hist_lo) * io.hist_scale);
+        if (ix >= 0 && ix < io.hist_bins && iy >= 0 && iy < io.hist_bins)
+          atomicAdd(&io.hist[ix * io.hist_bins + iy], 1ull);
+      }
+    } else {
+      m_n = m_s0 = m_s1 = m_s00 = m_s01 = m_s11 = 0;
+    }
+    m_n = lmc_warp_sum(m_n); m_s0 = lmc_warp_sum(m_s0); m_s1 = lmc_warp_sum(m_s1);
+    m_s00 = lmc_warp_sum(m_s00); m_s01 = lmc_warp_sum(m_s01); m_s11 = lmc_warp_sum(m_s11);
+    if (lane == 0) {
+      double* p = io.partial + (size_t)item * 6;
+      p[0] = m_n; p[1] = m_s0; p[2] = m_s1; p[3] = m_s00; p[4] = m_s01; p[5] = m_s11;
+    }
+  }
+}
+
+// fixed-order reduction of the per-item partials -> moments (deterministic)
+__global__ void __launch_bounds__(256) mix_reduce_moments(const double* __restrict__ partial, int n_items,
+                                                          double* __restrict__ out) {
+  __shared__ double sm[256][6];
+  double acc[6] = {0, 0, 0, 0, 0, 0};
+  for (int i = threadIdx.x; i < n_items; i += 256)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) acc[j] += partial[(size_t)i * 6 + j];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) sm[threadIdx.x][j] = acc[j];
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if ((int)threadIdx.x < s)
+#pragma unroll
+      for (int j = 0; j < 6; ++j) sm[threadIdx.x][j] += sm[threadIdx.x + s][j];
+    __syncthreads();
+  }
+  if (threadIdx.x < 6) out[threadIdx.x] += sm[0][threadIdx.x];
+}
+
+template <typename real>
+__global__ void philox_draws_kernel(int adjusted, long long C, long long K, uint2 key,
+                                    unsigned long long chain_offset, real* normals, real* unif, real* theta0) {
+  using M = Math<real>;
+  long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  unsigned long long gc = chain_offset + (unsigned long long)c;
+  uint32_t c_lo = (uint32_t)gc, c_hi = (uint32_t)(gc >> 32);
+  if (theta0 != nullptr) {
+    uint4 r = lmc_philox4x32_10(make_uint4(0u, LMC_STREAM_INIT, c_lo, c_hi), key);
+    M::normals(r.x, r.y, theta0[2 * c], theta0[2 * c + 1]);
+  }
+  uint4 rnd = make_uint4(0, 0, 0, 0);
+  for (long long k = 0; k < K; ++k) {
+    real x0, x1;
+    if (adjusted) {
+      rnd = lmc_philox4x32_10(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), key);
+      M::normals(rnd.x, rnd.y, x0, x1);
+      if (unif != nullptr) unif[c * K + k] = M::uniform(rnd.z);
+    } else if ((k & 1) == 0) {
+      long long kb = k >> 1;
+      rnd = lmc_philox4x32_10(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), key);
+      M::normals(rnd.x, rnd.y, x0, x1);
+    } else {
+      M::normals(rnd.z, rnd.w, x0, x1);
+    }
+    normals[(c * K + k) * 2] = x0;
+    normals[(c * K + k) * 2 + 1] = x1;
+  }
+}
+
+// ----------------------------------------------------------------------------------
+// host side
+template <typename real>
+void fill_params(const lmc_mix_target& T, const lmc_mix_step& S, MixP<real>& P) {
+  memset(&P, 0, sizeof(P));
+  P.n = T.n;
+  P.t = S.t;
+  for (int i = 0; i < T.n; ++i) {
+    P.mu0[i] = (real)T.mu[i][0];
+    P.mu1[i] = (real)T.mu[i][1];
+    P.p00[i] = (real)T.prec[i][0]; P.p01[i] = (real)T.prec[i][1];
+    P.p10[i] = (real)T.prec[i][2]; P.p11[i] = (real)T.prec[i][3];
+    P.al[i] = (real)T.alpha[i];
+    P.thr[i] = (real)(T.lamda * T.alpha[i]);
+    double cst = (T.kind == LMC_TARGET_LAPLACE) ? T.omega[i] * (T.alpha[i] / 2) * (T.alpha[i] / 2)
+                                                : T.omega[i] / T.norm[i];
+    P.lc[i] = (real)log2(cst);
+  }
+  P.lamda = (real)T.lamda;
+  P.inv_lamda = (real)(T.lamda != 0 ? 1.0 / T.lamda : 0.0);
+  P.pr_alpha = (real)T.prior_alpha;
+  P.pr_thr = (real)(T.lamda * T.prior_alpha);
+  P.pr_mu0 = (real)T.prior_mu[0];
+  P.pr_mu1 = (real)T.prior_mu[1];
+  P.gamma = (real)S.gamma;
+  P.s2g = (real)sqrt(2 * S.gamma);
+  P.inv4g = (real)(1.0 / (4 * S.gamma));
+  P.m00 = (real)S.M[0]; P.m01 = (real)S.M[1]; P.m10 = (real)S.M[2]; P.m11 = (real)S.M[3];
+  P.s00 = (real)S.sqrtM[0]; P.s01 = (real)S.sqrtM[1]; P.s10 = (real)S.sqrtM[2]; P.s11 = (real)S.sqrtM[3];
+  P.q00 = (real)S.Q[0]; P.q01 = (real)S.Q[1]; P.q10 = (real)S.Q[2]; P.q11 = (real)S.Q[3];
+  P.qi00 = (real)S.Qinv[0]; P.qi01 = (real)S.Qinv[1]; P.qi10 = (real)S.Qinv[2]; P.qi11 = (real)S.Qinv[3];
+  P.eta = (real)S.eta;
+  P.inv_eta = (real)(S.eta != 0 ? 1.0 / S.eta : 0.0);
+  P.pp_thr = (real)(S.eta != 0 ? T.lamda / S.eta : 0.0);
+  P.b0 = (real)S.beta[0]; P.b1 = (real)S.beta[1];
+  P.sg0 = (real)S.sigma[0]; P.sg1 = (real)S.sigma[1];
+  P.hshift = (real)S.hess_shift;
+}
+
+template <typename real, int TARGET, int ALG, int NC>
+int launch_one(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
+  auto kern = mix_chain_kernel<real, TARGET, ALG, NC>;
+  int dev = 0, sms = 0, occ = 0;
+  LMC_CUDA_OK(cudaGetDevice(&dev));
+  LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  LMC_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, BLOCK, 0));
+  if (occ < 1) occ = 1;
+  long long want = (io.n_items + (BLOCK / 32) - 1) / (BLOCK / 32);
+  long long cap = (long long)sms * occ;
+  int grid = (int)(want < cap ? want : cap);
+  if (grid < 1) grid = 1;
+  kern<<<grid, BLOCK, 0, st>>>(P, io);
+  LMC_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+template <typename real, int TARGET, int ALG>
+int launch_nc(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
+  if (P.n == 5) return launch_one<real, TARGET, ALG, 5>(P, io, st);
+  return launch_one<real, TARGET, ALG, 0>(P, io, st);
+}
+
+template <typename real>
+int dispatch(const lmc_mix_target& T, const lmc_mix_step& S, const MixIo& io, cudaStream_t st) {
+  MixP<real> P;
+  fill_params(T, S, P);
+#define LMC_CASE(TG, AL) \
+  if (T.kind == TG && S.alg == AL) return launch_nc<real, TG, AL>(P, io, st);
+  LMC_CASE(LMC_TARGET_GAUSS, LMC_ULA)
+  LMC_CASE(LMC_TARGET_GAUSS, LMC_MALA)
+  LMC_CASE(LMC_TARGET_GAUSS, LMC_PULA)
+  LMC_CASE(LMC_TARGET_GAUSS, LMC_IHPULA)
+  LMC_CASE(LMC_TARGET_GAUSS, LMC_MLA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_ULA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_MALA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_PULA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_IHPULA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_MLA)
+  LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_PGLD)
+  LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_MYULA)
+  LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_MYMALA)
+  LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_PPULA)
+  LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_FBULA)
+  LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_LBMUMLA)
+#undef LMC_CASE
+  lmc_set_error("lmc_mix_run: sampler %d is not defined for target kind %d", S.alg, T.kind);
+  return -1;
+}
+
+inline uint2 make_key(uint64_t seed) { return make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)); }
+
+}  // namespace
+
+extern "C" size_t lmc_mix_workspace_bytes(int64_t C) {
+  size_t items = (size_t)((C + 31) / 32);
+  return 256 + items * 6 * sizeof(double);
+}
+
+extern "C" int lmc_mix_run(const lmc_mix_target* target, const lmc_mix_step* step, int dtype, int64_t C,
+                           int64_t K, uint64_t seed, uint64_t chain_offset, const lmc_mix_io* uio,
+                           void* stream) {
+  LMC_REQUIRE(target && step && uio, "lmc_mix_run: null descriptor");
+  LMC_REQUIRE(dtype == LMC_F32 || dtype == LMC_F64, "lmc_mix_run: dtype must be LMC_F32 or LMC_F64");
+  LMC_REQUIRE(target->n >= 1 && target->n <= LMC_MAX_COMP, "lmc_mix_run: n=%d outside 1..%d", target->n,
+              LMC_MAX_COMP);
+  LMC_REQUIRE(C >= 0 && K >= 0, "lmc_mix_run: negative C or K");
+  LMC_REQUIRE(C < ((int64_t)1 << 36), "lmc_mix_run: C too large");
+  LMC_REQUIRE(step->gamma > 0, "lmc_mix_run: gamma must be positive");
+  if (C == 0) return 0;
+  LMC_REQUIRE(uio->d_theta != nullptr, "lmc_mix_run: d_theta is required");
+  LMC_REQUIRE(uio->d_workspace != nullptr && uio->workspace_bytes >= lmc_mix_workspace_bytes(C),
+              "lmc_mix_run: workspace too small (%zu < %zu)", uio->workspace_bytes,
+              lmc_mix_workspace_bytes(C));
+  const bool adj = step->alg == LMC_MALA || step->alg == LMC_MYMALA;
+  LMC_REQUIRE(!(uio->d_noise != nullptr && adj && uio->d_uniforms == nullptr),
+              "lmc_mix_run: adjusted samplers in validation mode need d_uniforms");
+  LMC_REQUIRE(!(uio->d_noise != nullptr && uio->init_from_rng),
+              "lmc_mix_run: validation mode takes the start state from d_theta");
+  LMC_REQUIRE(!(step->alg == LMC_PPULA && (step->t < 1 || !(step->eta > 0))),
+              "lmc_mix_run: PPULA needs t >= 1 and eta > 0");
+  LMC_REQUIRE(!(uio->d_hist != nullptr && (uio->hist_bins < 1 || !(uio->hist_hi > uio->hist_lo))),
+              "lmc_mix_run: bad histogram range");
+  cudaStream_t st = (cudaStream_t)stream;
+
+  MixIo io;
+  memset(&io, 0, sizeof(io));
+  io.theta = uio->d_theta;
+  io.noise = uio->d_noise;
+  io.unif = uio->d_uniforms;
+  io.traj = uio->d_traj;
+  io.accept = uio->d_accept;
+  io.naccept = uio->d_naccept;
+  io.hist = uio->d_hist;
+  io.queue = (unsigned int*)uio->d_workspace;
+  io.partial = (double*)((char*)uio->d_workspace + 256);
+  io.C = C;
+  io.K = K;
+  io.burnin = uio->burnin;
+  io.hist_every = uio->hist_every;
+  io.chain_offset = chain_offset;
+  io.key = make_key(seed);
+  io.init_from_rng = uio->init_from_rng;
+  io.hist_bins = uio->hist_bins;
+  io.hist_lo = uio->hist_lo;
+  io.hist_scale = uio->d_hist ? uio->hist_bins / (uio->hist_hi - uio->hist_lo) : 0.0;
+  io.n_items = (int)((C + 31) / 32);
+
+  LMC_CUDA_OK(cudaMemsetAsync(io.queue, 0, 256, st));
+  int rc = dtype == LMC_F64 ? dispatch<double>(*target, *step, io, st) : dispatch<float>(*target, *step, io, st);
+  if (rc != 0) return rc;
+  if (uio->d_moments != nullptr) {
+    mix_reduce_moments<<<1, 256, 0, st>>>(io.partial, io.n_items, uio->d_moments);
+    LMC_CUDA_OK(cudaGetLastError());
+  }
+  return 0;
+}
+
+extern "C" int lmc_mix_philox_draws(int dtype, int adjusted, int64_t C, int64_t K, uint64_t seed,
+                                    uint64_t chain_offset, void* d_normals, void* d_uniforms, void* d_theta0,
+                                    void* stream) {
+  LMC_REQUIRE(d_normals != nullptr, "lmc_mix_philox_draws: d_normals is required");
+  if (C <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = (int)((C + 127) / 128);
+  if (dtype == LMC_F64)
+    philox_draws_kernel<double><<<grid, 128, 0, st>>>(adjusted, C, K, make_key(seed), chain_offset,
+                                                      (double*)d_normals, (double*)d_uniforms, (double*)d_theta0);
+  else
+    philox_draws_kernel<float><<<grid, 128, 0, st>>>(adjusted, C, K, make_key(seed), chain_offset,
+                                                     (float*)d_normals, (float*)d_uniforms, (float*)d_theta0);
+  LMC_CUDA_OK(cudaGetLastError());
+  return 0;
+}
