@@ -259,7 +259,8 @@ def run_ours(args):
             "note": "register-resident chains: no HBM traffic in steady state, so the bound is FP32/INT32 issue "
                     "(north_star); algorithmic lane-ops per step from lmc_atomi_b200/roofline.py",
             "per_sampler": per_alg}
-    cpu = cpu_sample(k_unadj=args.cpu_steps, k_adj=max(args.cpu_steps // 4, 50)) if world == 1 else None
+    cpu = (cpu_sample(k_unadj=args.cpu_steps, k_adj=max(args.cpu_steps // 4, 50))
+           if (world == 1 and not args.no_cpu) else None)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
@@ -296,6 +297,7 @@ def main():
     ap.add_argument("--K", type=int, default=50000)
     ap.add_argument("--cpu-steps", type=int, default=3000)
     ap.add_argument("--no-image", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
