@@ -121,6 +121,93 @@ int lmc_mix_philox_draws(int dtype, int adjusted, int64_t C, int64_t K, uint64_t
                          uint64_t chain_offset, void* d_normals, void* d_uniforms,
                          void* d_theta0, void* stream);
 
+/* ------------------------------------------------------------------ image chains */
+#define LMC_IMG_MAX_TAPS 16
+
+/* Deconvolution problem: data term sigma_l2/2 ||H x - b||^2 with H a separable 2-D
+ * filter, zero boundary -- pylops.signalprocessing.Convolve2D((ny,nx), h, offset)
+ * (prox_lmc_deconv.py:55-69) wrapped in pyproximal.L2 (prox_lmc_deconv.py:101-103).
+ * Per axis the forward operator is out[i] = sum_t w[t] * in[i + lo + t] with
+ * -(ntap-1) <= lo <= 0; the adjoint is derived from the same taps. */
+typedef struct lmc_img_problem {
+  int32_t ny, nx;
+  int32_t ntap_y, ntap_x;
+  int32_t lo_y, lo_x;
+  double wy[LMC_IMG_MAX_TAPS], wx[LMC_IMG_MAX_TAPS];
+  double sigma_l2;          /* pyproximal.L2 sigma = 1 / sigma_noise^2 */
+  const void* d_b;          /* observation, (P,) shared by all chains or (C,P) */
+  int64_t b_chain_stride;   /* 0 = shared, P = per chain */
+} lmc_img_problem;
+
+/* MoreauYosidaUnadjustedLangevin(proxf=L2, proxg=TV(dims, tv_sigma, tv_niter, tv_rtol),
+ * tau, gamma, epsg)  (algs.py:477-587) */
+typedef struct lmc_img_myula_params {
+  double tau, gamma, epsg;
+  double tv_sigma, tv_rtol;
+  int32_t tv_niter;
+} lmc_img_myula_params;
+
+/* UnadjustedLangevinPrimalDual(proxf=L2(niter=lsqr_iter_lim, warm), proxg=L21|L1(sigma=g_sigma),
+ * A=Gradient, tau, mu, theta, gfirst)  (algs.py:295-474) */
+typedef struct lmc_img_ulpda_params {
+  double tau, mu, theta;
+  double g_sigma;           /* pyproximal.L21 / L1 sigma */
+  int32_t g_isotropic;      /* 1 = L21(ndim=2) (prox_lmc_deconv.py:116), 0 = L1 (:119) */
+  int32_t gfirst;           /* algs.py:435-448 */
+  int32_t lsqr_iter_lim;    /* pyproximal.L2 niter (50) */
+  int32_t warm;             /* pyproximal.L2 warm start */
+  double lsqr_atol, lsqr_btol, lsqr_conlim;   /* scipy lsqr defaults 1e-6, 1e-6, 1e8 */
+} lmc_img_ulpda_params;
+
+/* Buffers of one run of C image chains x N sampler iterations.  NULL = not requested. */
+typedef struct lmc_img_io {
+  void* d_x;                /* (C,P) in/out sampler state */
+  void* d_y;                /* (C,2,P) in/out ULPDA dual state (ignored by MYULA) */
+  void* d_xhat;             /* (C,P) in/out ULPDA extrapolated point */
+  void* d_warm;             /* (C,P) in/out LSQR warm start (pyproximal.L2.x0) */
+  const void* d_z;          /* (P,) optional ULPDA linear term z (algs.py:437-446), shared */
+  const void* d_noise;      /* (C,N,P) validation mode: host-supplied N(0,1); NULL = Philox */
+  void* d_samples;          /* (C,N,P) every sample (the reference's return value) */
+  void* d_ysamples;         /* (C,N,2,P) ULPDA returny */
+  void* d_mean;             /* (C,P) running posterior mean (Welford), updated in place */
+  void* d_m2;               /* (C,P) running sum of squared deviations */
+  unsigned long long* d_counters; /* (8,) added to: [0] TV sweeps, [1] LSQR iterations, [2] LSQR solves */
+  void* d_workspace;
+  size_t workspace_bytes;
+  int64_t burnin;           /* global iterations excluded from mean/m2 */
+  int64_t stat_count0;      /* samples already folded into mean/m2 (chunked runs) */
+  uint64_t iter_offset;     /* global index of this call's first iteration (Philox counter) */
+} lmc_img_io;
+
+size_t lmc_img_myula_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C);
+size_t lmc_img_ulpda_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C);
+
+/* C chains x N iterations in ONE persistent cooperative launch.  Chain c draws its
+ * noise from Philox4x32-10 keyed by seed with counter (pixel-quad, iteration,
+ * c + chain_offset), so results do not depend on the sharding over GPUs. */
+int lmc_img_myula_run(const lmc_img_problem* pb, const lmc_img_myula_params* pr, int dtype, int64_t C,
+                      int64_t N, uint64_t seed, uint64_t chain_offset, const lmc_img_io* io, void* stream);
+int lmc_img_ulpda_run(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, int dtype, int64_t C,
+                      int64_t N, uint64_t seed, uint64_t chain_offset, const lmc_img_io* io, void* stream);
+
+/* Unit entry points (operators of SURVEY 8a rows I1-I5), batched over C images.
+ * d_in/d_out are (C,P) unless stated; workspace as for the sampler of the same family. */
+int lmc_img_blur(const lmc_img_problem* pb, int dtype, int adjoint, int64_t C, const void* d_in, void* d_out,
+                 void* stream);                                   /* Convolve2D matvec / rmatvec */
+int lmc_img_grad(int dtype, int32_t ny, int32_t nx, int adjoint, int64_t C, const void* d_in, void* d_out,
+                 void* stream);                                   /* Gradient: (C,P)->(C,2,P) / adjoint */
+int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, int32_t niter, double rtol, int64_t C,
+                    const void* d_in, void* d_out, unsigned long long* d_counters, void* d_workspace,
+                    size_t workspace_bytes, void* stream);        /* pyproximal.TV.prox with sigma*tau = gamma */
+int lmc_img_proxdual(int dtype, int isotropic, double sigma, int64_t n_pix, void* d_v, void* stream);
+                                                                  /* L21/L1 proxdual, in place on (2,n_pix) */
+int lmc_img_l2_prox(const lmc_img_problem* pb, int dtype, double tau, int32_t iter_lim, double atol, double btol,
+                    double conlim, int64_t C, const void* d_in, void* d_warm, void* d_out,
+                    unsigned long long* d_counters, void* d_workspace, size_t workspace_bytes,
+                    void* stream);                                /* pyproximal.L2.prox (LSQR, warm start) */
+int lmc_img_noise(int dtype, int32_t ny, int32_t nx, int64_t C, int64_t N, uint64_t seed, uint64_t chain_offset,
+                  uint64_t iter_offset, void* d_out, void* stream); /* test hook: the Philox normals (C,N,P) */
+
 #ifdef __cplusplus
 }
 #endif

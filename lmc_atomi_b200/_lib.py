@@ -55,6 +55,36 @@ class MixIo(C.Structure):
                 ("hist_every", C.c_int64), ("burnin", C.c_int64)]
 
 
+IMG_MAX_TAPS = 16
+
+
+class ImgProblem(C.Structure):
+    _fields_ = [("ny", C.c_int32), ("nx", C.c_int32), ("ntap_y", C.c_int32), ("ntap_x", C.c_int32),
+                ("lo_y", C.c_int32), ("lo_x", C.c_int32),
+                ("wy", C.c_double * IMG_MAX_TAPS), ("wx", C.c_double * IMG_MAX_TAPS),
+                ("sigma_l2", C.c_double), ("d_b", C.c_void_p), ("b_chain_stride", C.c_int64)]
+
+
+class ImgMyulaParams(C.Structure):
+    _fields_ = [("tau", C.c_double), ("gamma", C.c_double), ("epsg", C.c_double),
+                ("tv_sigma", C.c_double), ("tv_rtol", C.c_double), ("tv_niter", C.c_int32)]
+
+
+class ImgUlpdaParams(C.Structure):
+    _fields_ = [("tau", C.c_double), ("mu", C.c_double), ("theta", C.c_double), ("g_sigma", C.c_double),
+                ("g_isotropic", C.c_int32), ("gfirst", C.c_int32), ("lsqr_iter_lim", C.c_int32),
+                ("warm", C.c_int32), ("lsqr_atol", C.c_double), ("lsqr_btol", C.c_double),
+                ("lsqr_conlim", C.c_double)]
+
+
+class ImgIo(C.Structure):
+    _fields_ = [("d_x", C.c_void_p), ("d_y", C.c_void_p), ("d_xhat", C.c_void_p), ("d_warm", C.c_void_p),
+                ("d_z", C.c_void_p), ("d_noise", C.c_void_p), ("d_samples", C.c_void_p),
+                ("d_ysamples", C.c_void_p), ("d_mean", C.c_void_p), ("d_m2", C.c_void_p),
+                ("d_counters", C.c_void_p), ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+                ("burnin", C.c_int64), ("stat_count0", C.c_int64), ("iter_offset", C.c_uint64)]
+
+
 # name -> (restype, argtypes); must list every symbol include/lmc_b200.h declares
 SIGNATURES = {
     "lmc_last_error": (C.c_char_p, []),
@@ -65,6 +95,24 @@ SIGNATURES = {
                               C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(MixIo), C.c_void_p]),
     "lmc_mix_philox_draws": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_uint64,
                                        C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lmc_img_myula_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int32, C.c_int32, C.c_int64]),
+    "lmc_img_ulpda_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int32, C.c_int32, C.c_int64]),
+    "lmc_img_myula_run": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgMyulaParams), C.c_int, C.c_int64,
+                                    C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),
+    "lmc_img_ulpda_run": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgUlpdaParams), C.c_int, C.c_int64,
+                                    C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),
+    "lmc_img_blur": (C.c_int, [C.POINTER(ImgProblem), C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,
+                               C.c_void_p]),
+    "lmc_img_grad": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,
+                               C.c_void_p]),
+    "lmc_img_tv_prox": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_int32, C.c_double, C.c_int64,
+                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lmc_img_proxdual": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int64, C.c_void_p, C.c_void_p]),
+    "lmc_img_l2_prox": (C.c_int, [C.POINTER(ImgProblem), C.c_int, C.c_double, C.c_int32, C.c_double, C.c_double,
+                                  C.c_double, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lmc_img_noise": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_uint64, C.c_uint64,
+                                C.c_uint64, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

@@ -1,0 +1,117 @@
+// Host side of img_myula.cu: workspace layout, argument marshalling, C entry points.
+#include "img_host_common.inl"
+
+namespace {
+
+template <typename real>
+size_t myula_ws_bytes(int ny, int nx, long long C) {
+  const size_t P = (size_t)ny * nx;
+  const size_t tiles = (size_t)((ny + TH - 1) / TH) * ((nx + TW - 1) / TW);
+  return 256 /* n_active + counters */ + align_up(C * sizeof(TvState)) + align_up(C * tiles * sizeof(double)) +
+         align_up((size_t)C * P * sizeof(real)) /* grad */ + align_up((size_t)6 * C * P * sizeof(real)) /* duals */;
+}
+
+template <typename real>
+int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long long C, long long N, uint64_t seed,
+              uint64_t chain_offset, const lmc_img_io* io, int mode, const void* tv_in, void* tv_out,
+              cudaStream_t st) {
+  MyulaArgs<real> A;
+  memset(&A, 0, sizeof(A));
+  fill_geom(pb, A.g);
+  const size_t need = myula_ws_bytes<real>(pb->ny, pb->nx, C);
+  LMC_REQUIRE(io->d_workspace != nullptr && io->workspace_bytes >= need, "image workspace too small (%zu < %zu)",
+              io->workspace_bytes, need);
+  char* ws = (char*)io->d_workspace;
+  A.n_active = (int*)ws;
+  unsigned long long* local_counters = (unsigned long long*)(ws + 64);
+  ws += 256;
+  A.st = (TvState*)ws;
+  ws += align_up(C * sizeof(TvState));
+  A.partial = (double*)ws;
+  ws += align_up((size_t)C * A.g.tiles * sizeof(double));
+  A.grad = (real*)ws;
+  ws += align_up((size_t)C * A.g.P * sizeof(real));
+  A.D = (real*)ws;
+  A.counters = io->d_counters ? io->d_counters : local_counters;
+  A.C = C;
+  A.N = N;
+  A.mode = mode;
+  A.key = img_key(seed);
+  A.chain_offset = chain_offset;
+  A.iter_offset = io->iter_offset;
+  A.burnin = io->burnin;
+  A.stat_count0 = io->stat_count0;
+  A.tv_niter = pr->tv_niter;
+  A.tv_rtol = pr->tv_rtol;
+  if (mode == 0) {
+    A.x = (real*)io->d_x;
+    A.b = (const real*)pb->d_b;
+    A.b_stride = pb->b_chain_stride;
+    A.noise = (const real*)io->d_noise;
+    A.samples = (real*)io->d_samples;
+    A.mean = (real*)io->d_mean;
+    A.m2 = (real*)io->d_m2;
+    A.sigma_l2 = (real)pb->sigma_l2;
+    A.tau = (real)pr->tau;
+    A.a_x = (real)(1 - pr->tau / pr->gamma);
+    A.tog = (real)(pr->tau / pr->gamma);
+    A.s2t = (real)sqrt(2 * pr->tau);
+    A.tv_gamma = (real)(pr->tv_sigma * (pr->epsg * pr->gamma));   // TV.prox(x, epsg*gamma): sigma * tau
+  } else {
+    A.x = (real*)const_cast<void*>(tv_in);
+    A.out = (real*)tv_out;
+    A.tv_gamma = (real)pr->tv_sigma;   // caller passes gamma = sigma * tau here
+  }
+  LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
+  return launch_persistent(img_myula_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);
+}
+
+}  // namespace
+
+extern "C" size_t lmc_img_myula_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C) {
+  if (ny < 1 || nx < 1 || C < 1) return 256;
+  return dtype == LMC_F64 ? myula_ws_bytes<double>(ny, nx, C) : myula_ws_bytes<float>(ny, nx, C);
+}
+
+extern "C" int lmc_img_myula_run(const lmc_img_problem* pb, const lmc_img_myula_params* pr, int dtype, int64_t C,
+                                 int64_t N, uint64_t seed, uint64_t chain_offset, const lmc_img_io* io,
+                                 void* stream) {
+  if (check_problem(pb, "lmc_img_myula_run") != 0) return -1;
+  LMC_REQUIRE(pr != nullptr && io != nullptr, "lmc_img_myula_run: null descriptor");
+  LMC_REQUIRE(dtype == LMC_F32 || dtype == LMC_F64, "lmc_img_myula_run: dtype must be LMC_F32 or LMC_F64");
+  LMC_REQUIRE(C >= 0 && N >= 0, "lmc_img_myula_run: negative C or N");
+  LMC_REQUIRE(pr->tau > 0 && pr->gamma > 0, "lmc_img_myula_run: tau and gamma must be positive");
+  LMC_REQUIRE(pr->tv_niter >= 0 && pr->tv_sigma * pr->epsg * pr->gamma > 0,
+              "lmc_img_myula_run: TV needs niter >= 0 and sigma*epsg*gamma > 0");
+  if (C == 0 || N == 0) return 0;
+  LMC_REQUIRE(io->d_x != nullptr && pb->d_b != nullptr, "lmc_img_myula_run: d_x and d_b are required");
+  LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
+              "lmc_img_myula_run: b_chain_stride must be 0 or ny*nx");
+  cudaStream_t st = (cudaStream_t)stream;
+  return dtype == LMC_F64 ? run_myula<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st)
+                          : run_myula<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st);
+}
+
+extern "C" int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, int32_t niter, double rtol,
+                               int64_t C, const void* d_in, void* d_out, unsigned long long* d_counters,
+                               void* d_workspace, size_t workspace_bytes, void* stream) {
+  LMC_REQUIRE(dtype == LMC_F32 || dtype == LMC_F64, "lmc_img_tv_prox: bad dtype");
+  LMC_REQUIRE(ny >= 1 && nx >= 1 && C >= 0 && niter >= 0 && gamma > 0, "lmc_img_tv_prox: bad arguments");
+  if (C == 0) return 0;
+  LMC_REQUIRE(d_in != nullptr && d_out != nullptr, "lmc_img_tv_prox: null buffer");
+  lmc_img_problem pb;
+  identity_problem(pb, ny, nx);
+  lmc_img_myula_params pr;
+  memset(&pr, 0, sizeof(pr));
+  pr.tv_sigma = gamma;
+  pr.tv_niter = niter;
+  pr.tv_rtol = rtol;
+  lmc_img_io io;
+  memset(&io, 0, sizeof(io));
+  io.d_workspace = d_workspace;
+  io.workspace_bytes = workspace_bytes;
+  io.d_counters = d_counters;
+  cudaStream_t st = (cudaStream_t)stream;
+  return dtype == LMC_F64 ? run_myula<double>(&pb, &pr, C, 1, 0, 0, &io, 1, d_in, d_out, st)
+                          : run_myula<float>(&pb, &pr, C, 1, 0, 0, &io, 1, d_in, d_out, st);
+}

@@ -1,0 +1,271 @@
+"""GPU parity tests of the image (deconvolution) path against the CPU oracle
+(oracle/deconv_ref.py): unit operators, TV prox, LSQR-solved L2 prox, and the MYULA /
+ULPDA trajectories on the same inputs and the same noise.
+
+Tolerances (north_star): fp64 mode 1e-12 relative, fp32 mode 1e-5 relative, both
+normalised by the dynamic range of the compared array (images live in [0, 255])."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [(64, 64), (40, 52), (33, 95)]     # tile-aligned, ragged, ragged with nx % 4 != 0
+
+
+def rel(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(1.0, np.abs(b).max()))
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    return torch
+
+
+def dev_t(torch, a, dtype="float64"):
+    return torch.as_tensor(np.ascontiguousarray(a)).to("cuda", torch.float64 if dtype == "float64" else torch.float32)
+
+
+# --------------------------------------------------------------------------- operators
+@pytest.mark.parametrize("k", [5, 6, 7])
+@pytest.mark.parametrize("dims", SIZES)
+def test_blur_matches_oracle(torch, k, dims):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    rng = np.random.default_rng(k)
+    h = np.ones((k, k)) / k ** 2
+    H = D.Convolve2D(dims, h, (k // 2, k // 2))
+    spec = I.BlurSpec(dims, I.pad_filter(h, (k // 2, k // 2)))
+    x = rng.standard_normal((3, dims[0] * dims[1])) * 50
+    xd = dev_t(torch, x)
+    got_f = I.blur(spec, xd).cpu().numpy()
+    got_a = I.blur(spec, xd, adjoint=True).cpu().numpy()
+    for c in range(3):
+        assert rel(got_f[c], H.matvec(x[c])) < 1e-13
+        assert rel(got_a[c], H.rmatvec(x[c])) < 1e-13
+    # adjoint identity on the device operators themselves
+    y = rng.standard_normal(dims[0] * dims[1])
+    lhs = float(got_f[0] @ y)
+    rhs = float(x[0] @ I.blur(spec, dev_t(torch, y), adjoint=True).cpu().numpy())
+    assert abs(lhs - rhs) < 1e-9 * max(1.0, abs(lhs))
+
+
+def test_blur_nonuniform_separable_filter(torch):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    dims = (37, 61)
+    h = np.outer([1., 2., 3.], [0.5, 1., 0.25, 2., 1.])
+    h /= h.sum()
+    H = D.Convolve2D(dims, h, (1, 2))
+    spec = I.BlurSpec(dims, I.pad_filter(h, (1, 2)))
+    x = np.random.default_rng(0).standard_normal(dims[0] * dims[1])
+    assert rel(I.blur(spec, dev_t(torch, x)).cpu().numpy(), H.matvec(x)) < 1e-13
+    assert rel(I.blur(spec, dev_t(torch, x), adjoint=True).cpu().numpy(), H.rmatvec(x)) < 1e-13
+    with pytest.raises(NotImplementedError):
+        I.BlurSpec(dims, np.array([[1., 2.], [3., 5.]]))     # rank 2: not separable
+
+
+@pytest.mark.parametrize("dims", SIZES)
+def test_gradient_matches_oracle(torch, dims):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    rng = np.random.default_rng(1)
+    G = D.Gradient(dims)
+    x = rng.standard_normal((2, dims[0] * dims[1]))
+    v = rng.standard_normal((2, 2 * dims[0] * dims[1]))
+    gf = I.grad(dims, dev_t(torch, x)).cpu().numpy().reshape(2, -1)
+    ga = I.grad(dims, dev_t(torch, v), adjoint=True).cpu().numpy()
+    for c in range(2):
+        assert np.array_equal(gf[c], G.matvec(x[c]))
+        assert rel(ga[c], G.rmatvec(v[c])) < 1e-15
+
+
+@pytest.mark.parametrize("iso", [True, False])
+def test_proxdual_matches_oracle(torch, iso):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    rng = np.random.default_rng(2)
+    v = rng.standard_normal((2, 5000)) * 0.6
+    op = D.L21(2, 0.3) if iso else D.L1(0.3)
+    want = op.proxdual(v.ravel().copy(), 1.0).reshape(2, -1)
+    got = I.proxdual(dev_t(torch, v), 0.3, isotropic=iso).cpu().numpy()
+    assert rel(got, want) < 1e-14
+
+
+# --------------------------------------------------------------------------- TV prox
+@pytest.mark.parametrize("dims", SIZES)
+@pytest.mark.parametrize("gamma,niter", [(0.16875, 10), (15.0, 50), (0.16875, 1)])
+def test_tv_prox_matches_oracle(torch, dims, gamma, niter):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    img = D.synthetic_image(*dims).astype(np.float64)
+    rng = np.random.default_rng(3)
+    xs = np.stack([img + rng.normal(0, s, img.shape) for s in (0.5, 5.0, 20.0)])
+    counters = torch.zeros(8, dtype=torch.int64, device="cuda")
+    got = I.tv_prox(dims, dev_t(torch, xs.reshape(3, -1)), gamma, niter, 1e-4, counters=counters).cpu().numpy()
+    sweeps = 0
+    for c in range(3):
+        want, nupd = D.tv_prox_2d(xs[c], gamma, niter, 1e-4)
+        sweeps += min(nupd + 1, niter)
+        assert rel(got[c], want.ravel()) < 1e-12, (c, nupd)
+    assert int(counters[0].item()) == sweeps     # per-chain early exit reproduced
+
+
+def test_tv_prox_zero_image(torch):
+    """x = 0 (first MYULA iteration from x0 = 0): obj <= 1e-10 never triggers the break."""
+    from lmc_atomi_b200 import imaging as I
+    got = I.tv_prox((48, 48), torch.zeros((1, 48 * 48), dtype=torch.float64, device="cuda"), 0.2, 10, 1e-4)
+    assert float(got.abs().max()) == 0.0
+
+
+# --------------------------------------------------------------------------- L2 prox (LSQR)
+@pytest.mark.parametrize("k", [5, 6])
+def test_l2_prox_matches_scipy_lsqr(torch, k):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    dims = (40, 52)
+    img = D.synthetic_image(*dims)
+    pb = D.build_problem(img, kernel=k)
+    l2 = pb["l2"]()
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    warm = torch.zeros((1, dims[0] * dims[1]), dtype=torch.float64, device="cuda")
+    rng = np.random.default_rng(4)
+    x = img.ravel().astype(np.float64)
+    for it in range(3):    # warm start carried across calls, as pyproximal.L2(warm=True) does
+        arg = x + rng.standard_normal(x.shape) * 3
+        want = l2.prox(arg.copy(), pb["tau0"])
+        got = eng.l2_prox(dev_t(torch, arg[None]), pb["tau0"], warm).cpu().numpy()[0]
+        assert rel(got, want) < 1e-11, it
+        x = want
+    c = eng.read_counters()
+    assert c["lsqr_iterations"] == sum(l2.lsqr_itn) and c["lsqr_solves"] == 3
+
+
+# --------------------------------------------------------------------------- samplers
+def _problem(dims, kernel=5):
+    from oracle import deconv_ref as D
+    img = D.synthetic_image(*dims)
+    return D.build_problem(img, kernel=kernel)
+
+
+@pytest.mark.parametrize("dims,kernel", [((64, 64), 5), ((40, 52), 5), ((33, 95), 6), ((64, 64), 7)])
+def test_myula_trajectory_fp64(torch, dims, kernel):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    N = 25
+    pb = _problem(dims, kernel)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(0, N, P)
+    tv = pb["tv"]()
+    want = D.MoreauYosidaUnadjustedLangevin(pb["l2"](), tv, pb["x0"], tau=pb["tau_myula"], gamma=pb["gamma_myula"],
+                                            niter=N, noise=noise)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    x = torch.zeros((1, P), dtype=torch.float64, device="cuda")
+    samples = torch.empty((1, N, P), dtype=torch.float64, device="cuda")
+    mean = torch.zeros((1, P), dtype=torch.float64, device="cuda")
+    m2 = torch.zeros((1, P), dtype=torch.float64, device="cuda")
+    eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise[None], samples=samples,
+              mean=mean, m2=m2)
+    got = samples.cpu().numpy()[0]
+    errs = [rel(got[n], want[n]) for n in range(N)]
+    assert max(errs) < 1e-12, errs
+    assert rel(mean.cpu().numpy()[0], want.mean(axis=0)) < 1e-12
+    assert rel(m2.cpu().numpy()[0] / N, want.var(axis=0)) < 1e-10
+    assert eng.read_counters()["tv_sweeps"] == sum(min(u + 1, 10) for u in tv.updates)
+
+
+@pytest.mark.parametrize("dims,kernel,iso,gfirst", [((64, 64), 5, True, False), ((40, 52), 5, False, False),
+                                                    ((33, 95), 6, True, True), ((64, 64), 7, True, False)])
+def test_ulpda_trajectory_fp64(torch, dims, kernel, iso, gfirst):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    N = 12
+    pb = _problem(dims, kernel)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(0, N, P)
+    l2 = pb["l2"]()
+    g = pb["l1iso"]() if iso else pb["l1"]()
+    want, wanty = D.UnadjustedLangevinPrimalDual(l2, g, pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], theta=1., niter=N,
+                                                 gfirst=gfirst, returny=True, noise=noise)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    z = lambda *s: torch.zeros(s, dtype=torch.float64, device="cuda")
+    x, xhat, y, warm = z(1, P), z(1, P), z(1, 2, P), z(1, P)
+    samples, ys = z(1, N, P), z(1, N, 2, P)
+    eng.ulpda(x, xhat, y, warm, N, pb["tau0"], pb["mu0"], 1.0, 0.3, iso, gfirst, 50, noise=noise[None],
+              samples=samples, ysamples=ys)
+    got = samples.cpu().numpy()[0]
+    errs = [rel(got[n], want[n]) for n in range(N)]
+    assert max(errs) < 1e-11, errs
+    assert rel(ys.cpu().numpy()[0].reshape(N, -1), wanty) < 1e-11
+    c = eng.read_counters()
+    assert c["lsqr_iterations"] == sum(l2.lsqr_itn), (c, l2.lsqr_itn)
+
+
+def test_myula_fp32_within_tolerance(torch):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    dims, N = (64, 64), 25
+    pb = _problem(dims)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(0, N, P)
+    want = D.MoreauYosidaUnadjustedLangevin(pb["l2"](), pb["tv"](), pb["x0"], tau=pb["tau_myula"],
+                                            gamma=pb["gamma_myula"], niter=N, noise=noise)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float32")
+    x = torch.zeros((1, P), dtype=torch.float32, device="cuda")
+    samples = torch.empty((1, N, P), dtype=torch.float32, device="cuda")
+    eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise[None], samples=samples)
+    got = samples.cpu().numpy()[0]
+    err = max(rel(got[n], want[n]) for n in range(N))
+    print(f"MYULA fp32 free-run rel err over {N} iterations: {err:.3e}")
+    assert err < 1e-5
+
+
+def test_ulpda_fp32_within_tolerance(torch):
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    dims, N = (64, 64), 12
+    pb = _problem(dims)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(0, N, P)
+    want = D.UnadjustedLangevinPrimalDual(pb["l2"](), pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"],
+                                          theta=1., niter=N, gfirst=False, noise=noise)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float32")
+    z = lambda *s: torch.zeros(s, dtype=torch.float32, device="cuda")
+    x, xhat, y, warm, samples = z(1, P), z(1, P), z(1, 2, P), z(1, P), z(1, N, P)
+    eng.ulpda(x, xhat, y, warm, N, pb["tau0"], pb["mu0"], 1.0, 0.3, True, False, 50, noise=noise[None],
+              samples=samples)
+    got = samples.cpu().numpy()[0]
+    err = max(rel(got[n], want[n]) for n in range(N))
+    print(f"ULPDA fp32 free-run rel err over {N} iterations: {err:.3e}")
+    # LSQR stops on atol=btol=1e-6: the solve itself is only 1e-6-accurate, so fp32 rounding can move
+    # the stopping iteration; the tolerance reflects the solver's own accuracy.
+    assert err < 2e-5
+
+
+def test_batched_chains_are_independent(torch):
+    """C chains with different noise == C separate single-chain runs (per-chain early exit)."""
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    dims, N, Cn = (40, 52), 8, 3
+    pb = _problem(dims)
+    P = dims[0] * dims[1]
+    noise = np.stack([D.image_noise(s, N, P) for s in range(Cn)])
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    x = torch.zeros((Cn, P), dtype=torch.float64, device="cuda")
+    samples = torch.empty((Cn, N, P), dtype=torch.float64, device="cuda")
+    eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise, samples=samples)
+    got = samples.cpu().numpy()
+    for c in range(Cn):
+        want = D.MoreauYosidaUnadjustedLangevin(pb["l2"](), pb["tv"](), pb["x0"], tau=pb["tau_myula"],
+                                                gamma=pb["gamma_myula"], niter=N, noise=noise[c])
+        assert rel(got[c], want) < 1e-12
+    z = lambda *s: torch.zeros(s, dtype=torch.float64, device="cuda")
+    x, xhat, y, warm, samples = z(Cn, P), z(Cn, P), z(Cn, 2, P), z(Cn, P), z(Cn, N, P)
+    eng.ulpda(x, xhat, y, warm, N, pb["tau0"], pb["mu0"], 1.0, 0.3, True, False, 50, noise=noise, samples=samples)
+    got = samples.cpu().numpy()
+    for c in range(Cn):
+        want = D.UnadjustedLangevinPrimalDual(pb["l2"](), pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"],
+                                              theta=1., niter=N, gfirst=False, noise=noise[c])
+        assert rel(got[c], want) < 1e-11
