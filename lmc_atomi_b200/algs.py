@@ -1,0 +1,219 @@
+"""Drop-in for the reference's ``algs`` module (the image samplers of algs.py:295-587):
+same function names, argument order, defaults, seed semantics and return shapes.  The
+per-iteration Python loops of the reference are replaced by launches of the persistent
+CUDA kernels behind include/lmc_b200.h; the operator objects (``proxf``, ``proxg``, ``A``)
+are read for their parameters by duck typing (real pylops / pyproximal objects or the
+stand-ins of ``compat``).  Unrecognised operator combinations raise NotImplementedError:
+there is no CPU fallback.
+
+Noise: the reference draws ``scipy.stats.multivariate_normal.rvs(size=x.shape,
+random_state=default_rng(seed))`` every iteration (algs.py:431-433, 561-565), which is
+``rng.standard_normal(P)`` bit for bit; the same stream is generated on the
+host and fed to the kernels, so for a given seed the samples follow the reference's
+trajectory (``philox=True`` switches to in-kernel counter-based noise instead).
+"""
+from __future__ import annotations
+
+import time
+
+import numpy as np
+from numpy.random import default_rng
+
+from . import _lib, imaging
+
+__all__ = ["MoreauYosidaUnadjustedLangevin", "UnadjustedLangevinPrimalDual", "L2_ncvx_tv"]
+
+CHUNK_BYTES = 1 << 30     # device staging for noise + samples per launch
+
+
+def _kind(obj):
+    return type(obj).__name__
+
+
+def _require(cond, msg):
+    if not cond:
+        raise NotImplementedError(msg + " (no CUDA path for this combination and no CPU fallback by design)")
+
+
+def _blur_of(proxf):
+    Op = getattr(proxf, "Op", None)
+    _require(Op is not None and hasattr(Op, "h") and hasattr(Op, "dims"),
+             "proxf.Op must be a Convolve2D-like operator exposing .h and .dims")
+    _require(getattr(proxf, "b", None) is not None, "proxf must carry data b")
+    _require(getattr(proxf, "q", None) is None and getattr(proxf, "alpha", 1.0) == 1.0,
+             "L2 with q/alpha terms")
+    dims = tuple(int(d) for d in Op.dims)
+    _require(len(dims) == 2, "2-D images")
+    return dims, np.asarray(Op.h, dtype=np.float64)
+
+
+def _engine(proxf, dtype):
+    _require(_kind(proxf) == "L2", f"proxf of type {_kind(proxf)}; supported: pyproximal.L2")
+    dims, h = _blur_of(proxf)
+    return imaging.DeconvEngine(dims, h, np.asarray(proxf.b, dtype=np.float64), float(proxf.sigma), dtype=dtype)
+
+
+def _chunk(niter, P, itemsize, arrays):
+    per_it = max(1, arrays * P * itemsize)
+    return int(max(1, min(niter, CHUNK_BYTES // per_it)))
+
+
+def _show_line(iiter, niter):
+    return iiter < 10 or niter - iiter < 10 or (niter >= 10 and iiter % (niter // 10) == 0)
+
+
+def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1., niter=10, seed=0,
+                                   callback=None, show=False, dtype="float64", philox=False):
+    """MYULA (algs.py:477-587):
+    x <- (1 - tau/gamma) x - tau grad f(x) + tau/gamma prox_{gamma epsg g}(x) + sqrt(2 tau) xi.
+    Returns the (niter, P) float64 array of samples, as the reference does."""
+    _require(tau is not None, "tau=None (the reference itself fails on it at algs.py:569)")
+    _require(np.asarray(epsg).size == 1, "vector epsg")
+    _require(_kind(proxg) == "TV", f"proxg of type {_kind(proxg)}; supported: pyproximal.TV")
+    eng = _engine(proxf, dtype)
+    torch = eng.torch
+    _require(tuple(int(d) for d in proxg.dims) == eng.dims, "TV dims must equal the image dims")
+    x0 = np.asarray(x0, dtype=np.float64)
+    P = eng.P
+    if show:
+        tstart = time.time()
+        print('Moreau--Yosida Unadjusted Langevin\n'
+              '---------------------------------------------------------\n'
+              'Proximal operator (f): %s\nProximal operator (g): %s\n'
+              'tau = %s\tgamma=%10e\nepsg = %s\tniter = %d\n'
+              % (type(proxf), type(proxg), str(tau), gamma, str(epsg), niter))
+        print('   Itn       x[0]          f           g     J = f + eps*g')
+    rng = default_rng(seed)
+    x = eng._buf(x0, 1)
+    out = np.empty((niter, P), dtype=np.float64)
+    per_iter = callback is not None or show
+    step = 1 if per_iter else _chunk(niter, P, x.element_size(), 2)
+    done = 0
+    while done < niter:
+        n = min(step, niter - done)
+        noise = None if philox else rng.standard_normal((1, n, P))
+        samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
+        keep = eng.myula(x, n, tau, gamma, float(proxg.sigma), int(proxg.niter), float(proxg.rtol),
+                         epsg=float(epsg), seed=seed, noise=noise, samples=samples, iter_offset=done)
+        out[done:done + n] = samples[0].double().cpu().numpy()   # synchronises the stream
+        del keep
+        if per_iter:
+            xh = out[done]
+            if callback is not None:
+                callback(xh)
+            if show and _show_line(done, niter):
+                pf, pg = proxf(xh), proxg(xh)
+                print('%6g  %12.5e  %10.3e  %10.3e  %10.3e' % (done + 1, xh[0], pf, pg, pf + epsg * pg))
+        done += n
+    if show:
+        print('\nTotal time (s) = %.2f' % (time.time() - tstart))
+        print('---------------------------------------------------------\n')
+    return out
+
+
+def _is_gradient(A, dims):
+    if _kind(A) not in ("Gradient", "VStack"):
+        return False
+    P = dims[0] * dims[1]
+    if tuple(getattr(A, "shape", ())) != (2 * P, P):
+        return False
+    return getattr(A, "kind", "forward") == "forward" and not getattr(A, "edge", False)
+
+
+def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, theta=1., niter=10,
+                                 seed=0, gfirst=True, callback=None, callbacky=False, returny=False,
+                                 show=False, dtype="float64", philox=False):
+    """ULPDA (algs.py:295-474) for U(x) = f(x) + x^T z + g(Ax) with f = L2 (prox by warm-started
+    LSQR), g = L21 / L1 (dual prox = projection), A = forward-difference Gradient.
+    Returns (niter, P) samples [and (niter, 2P) dual samples when ``returny``]."""
+    eng = _engine(proxf, dtype)
+    torch = eng.torch
+    P = eng.P
+    _require(_kind(proxg) in ("L21", "L1"), f"proxg of type {_kind(proxg)}; supported: pyproximal.L21, L1")
+    iso = _kind(proxg) == "L21"
+    _require(not iso or int(getattr(proxg, "ndim", 2)) == 2, "L21 with ndim != 2")
+    _require(getattr(proxg, "g", None) is None, "L1 with a shift vector")
+    _require(_is_gradient(A, eng.dims), "A must be pylops.Gradient(dims, kind='forward', edge=False)")
+    x0 = np.asarray(x0, dtype=np.float64)
+    # algs.py:401-408: scalars become constant arrays
+    fixedtau, fixedmu = isinstance(tau, (int, float)), isinstance(mu, (int, float))
+    tau = tau * np.ones(niter, dtype=x0.dtype) if fixedtau else np.asarray(tau, dtype=np.float64)
+    mu = mu * np.ones(niter, dtype=x0.dtype) if fixedmu else np.asarray(mu, dtype=np.float64)
+    constant = bool(np.all(tau == tau[0]) and np.all(mu == mu[0])) if niter > 0 else True
+    if show:
+        tstart = time.time()
+        print('Unadjusted Langevin primal-dual: U(x) = f(x) + x^T z + g(Ax)\n'
+              '---------------------------------------------------------\n'
+              'Proximal operator (f): %s\nProximal operator (g): %s\nLinear operator (A): %s\n'
+              'Additional vector (z): %s\ntau = %s\t\tmu = %s\ntheta = %.2f\t\tniter = %d\n' %
+              (type(proxf), type(proxg), type(A), None if z is None else 'vector',
+               str(tau[0]) if fixedtau else 'Variable', str(mu[0]) if fixedmu else 'Variable', theta, niter))
+        print('   Itn       x[0]          f         g o A        z^x      U = f + g o A + z^x')
+    rng = default_rng(seed)
+    x = eng._buf(x0, 1)
+    xhat = x.clone()
+    y = eng._buf(y0, 1, inner=2) if y0 is not None else torch.zeros((1, 2, P), dtype=eng.tdt, device=eng.dev)
+    warm_on = bool(getattr(proxf, "warm", True))
+    warm = eng._buf(getattr(proxf, "x0", None) if warm_on else None, 1)
+    kw = getattr(proxf, "kwargs_solver", None) or {}
+    out = np.empty((niter, P), dtype=np.float64)
+    outy = np.empty((niter, 2 * P), dtype=np.float64) if returny else None
+    need_y = returny or (callback is not None and callbacky)
+    per_iter = callback is not None or show or not constant
+    step = 1 if per_iter else _chunk(niter, P, x.element_size(), 2 + (2 if need_y else 0))
+    done = 0
+    while done < niter:
+        n = min(step, niter - done)
+        noise = None if philox else rng.standard_normal((1, n, P))
+        samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
+        ys = torch.empty((1, n, 2, P), dtype=eng.tdt, device=eng.dev) if need_y else None
+        keep = eng.ulpda(x, xhat, y, warm, n, float(tau[done]), float(mu[done]), float(theta), float(proxg.sigma),
+                         iso, gfirst, int(proxf.niter), warm_start=warm_on, atol=kw.get("atol", 1e-6),
+                         btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=z, seed=seed, noise=noise,
+                         samples=samples, ysamples=ys, iter_offset=done)
+        out[done:done + n] = samples[0].double().cpu().numpy()
+        if need_y:
+            yh = ys[0].double().cpu().numpy().reshape(n, 2 * P)
+            if returny:
+                outy[done:done + n] = yh
+        del keep
+        if callback is not None:
+            if callbacky:
+                callback(out[done], yh[0])
+            else:
+                callback(out[done])
+        if show and _show_line(done, niter):
+            xh = out[done]
+            pf, pg = proxf(xh), proxg(A.matvec(xh))
+            pf = 0. if type(pf) == bool else pf
+            pg = 0. if type(pg) == bool else pg
+            zx = 0. if z is None else float(np.dot(z, xh))
+            print('%6g  %12.5e  %10.3e  %10.3e  %10.3e      %10.3e' % (done + 1, xh[0], pf, pg, zx, pf + pg + zx))
+        done += n
+    if warm_on and niter > 0:
+        proxf.x0 = warm[0].double().cpu().numpy()     # pyproximal.L2 keeps the last solution as warm start
+    if hasattr(proxf, "count"):
+        proxf.count += niter
+    if show:
+        print('\nTotal time (s) = %.2f' % (time.time() - tstart))
+        print('---------------------------------------------------------\n')
+    if not returny:
+        return out
+    return out, outy
+
+
+class L2_ncvx_tv:
+    """Parameter carrier for the reference's non-convex data term (algs.py:22-291):
+    sigma/2 ||Op x - b||^2 - lamda * env_gamma(TV)(x), MC-TV when ``Op2`` (the Gradient) is given,
+    ME-TV otherwise.  Same constructor as algs.py:129-131.  The samplers read its parameters."""
+
+    def __init__(self, dims, Op=None, Op2=None, b=None, q=None, sigma=1., alpha=1., lamda=1., gamma=.5,
+                 qgrad=True, isotropic=False, niter=10, rtol=1e-4, x0=None, warm=True, densesolver=None,
+                 kwargs_solver=None):
+        self.dims, self.ndim = tuple(dims), len(dims)
+        self.Op, self.Op2, self.b, self.q = Op, Op2, b, q
+        self.sigma, self.alpha, self.lamda, self.gamma = sigma, alpha, lamda, gamma
+        self.qgrad, self.isotropic, self.niter, self.rtol = qgrad, isotropic, niter, rtol
+        self.x0, self.warm, self.densesolver, self.count = x0, warm, densesolver, 0
+        self.kwargs_solver = {} if kwargs_solver is None else kwargs_solver
+        self.hasgrad = True

@@ -1,0 +1,221 @@
+"""Parameter-carrying stand-ins for the third-party objects the reference's image driver
+hands to ``algs`` (prox_lmc_deconv.py:55-125): ``pylops.signalprocessing.Convolve2D``,
+``pylops.Gradient``, ``pylops.Identity``, ``pyproximal.L2 / L1 / L21 / TV``.
+
+Neither library exists in this image, so a headless run of the driver needs
+objects with the same constructor arguments and attribute names.  They hold parameters; the
+few methods the driver's ``callback`` / ``show`` paths call (``matvec``, ``rmatvec``,
+``__call__``, ``prox``, ``grad``, ``proxdual``) are served by the CUDA unit operators of
+include/lmc_b200.h (host array in, host array out) -- there is no numpy implementation here.
+``algs`` reads real pylops/pyproximal objects by the same attribute names (duck typing).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import _lib, imaging
+
+
+def _dev(a, shape=None):
+    torch = _lib.require_cuda()
+    t = torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64)).cuda()
+    return t if shape is None else t.reshape(shape)
+
+
+class _LinOp:
+    def __mul__(self, x):
+        return self.matvec(x)
+
+    __matmul__ = __mul__
+
+    @property
+    def H(self):
+        return _Adjoint(self)
+
+
+class _Adjoint(_LinOp):
+    def __init__(self, op):
+        self.op = op
+        self.shape = op.shape[::-1]
+
+    def matvec(self, x):
+        return self.op.rmatvec(x)
+
+    def rmatvec(self, x):
+        return self.op.matvec(x)
+
+
+class Convolve2D(_LinOp):
+    """pylops.signalprocessing.Convolve2D(dims, h, offset) -- SURVEY 8a I1."""
+    explicit = False
+
+    def __init__(self, dims, h, offset=(0, 0), axes=(-2, -1), method="fft", dtype="float64", name="C"):
+        self.dims = tuple(int(d) for d in dims)
+        self.offset = tuple(int(o) for o in offset)
+        self.h = imaging.pad_filter(h, self.offset)
+        n = self.dims[0] * self.dims[1]
+        self.shape = (n, n)
+        self.dtype = np.dtype(dtype)
+        self._spec = imaging.BlurSpec(self.dims, self.h)
+
+    def _apply(self, x, adjoint):
+        x = np.asarray(x)
+        out = imaging.blur(self._spec, _dev(x, (1, -1)), adjoint=adjoint).cpu().numpy()
+        return out.reshape(x.shape)
+
+    def matvec(self, x):
+        return self._apply(x, False)
+
+    def rmatvec(self, x):
+        return self._apply(x, True)
+
+
+class Gradient(_LinOp):
+    """pylops.Gradient(dims, sampling=1, edge=False, kind='forward') -- SURVEY 8a I2."""
+    explicit = False
+
+    def __init__(self, dims, sampling=1, edge=False, kind="forward", dtype="float64", name="G"):
+        if kind != "forward" or edge or np.any(np.asarray(sampling, dtype=float) != 1.0):
+            raise NotImplementedError("the CUDA path covers Gradient(kind='forward', edge=False, sampling=1)")
+        self.dims = tuple(int(d) for d in dims)
+        self.sampling, self.edge, self.kind = sampling, edge, kind
+        n = self.dims[0] * self.dims[1]
+        self.shape = (2 * n, n)
+        self.dtype = np.dtype(dtype)
+
+    def matvec(self, x):
+        return imaging.grad(self.dims, _dev(x, (1, -1))).cpu().numpy().ravel()
+
+    def rmatvec(self, v):
+        return imaging.grad(self.dims, _dev(v, (1, 2, -1)), adjoint=True).cpu().numpy().ravel()
+
+
+class Identity(_LinOp):
+    explicit = False
+
+    def __init__(self, N, M=None, dtype="float64"):
+        self.shape = (int(N) if M is None else int(M), int(N))
+        self.dtype = np.dtype(dtype)
+
+    def matvec(self, x):
+        return x
+
+    rmatvec = matvec
+
+
+# --------------------------------------------------------------------------- proximal operators
+class ProxOperator:
+    def __init__(self, Op=None, hasgrad=False):
+        self.Op = Op
+        self.hasgrad = hasgrad
+
+    def proxdual(self, x, tau):
+        """Moreau identity (pyproximal ProxOperator._proxdual_moreau)."""
+        return x - tau * self.prox(x / tau, 1.0 / tau)
+
+
+class L1(ProxOperator):
+    """pyproximal.L1(sigma): anisotropic norm; dual prox = clip."""
+
+    def __init__(self, sigma=1.0, g=None):
+        super().__init__(None, False)
+        if g is not None:
+            raise NotImplementedError("L1 with a shift vector g is not on the reference's path")
+        self.sigma, self.g = sigma, g
+
+    def __call__(self, x):
+        return float(self.sigma * _dev(x).abs().sum().item())
+
+    def proxdual(self, x, tau):
+        v = _dev(x, (2, -1)).contiguous()
+        return imaging.proxdual(v, self.sigma, isotropic=False).cpu().numpy().reshape(np.shape(x))
+
+    def prox(self, x, tau):
+        x = np.asarray(x, dtype=np.float64)
+        return x - tau * self.proxdual(x / tau, 1.0 / tau)
+
+
+class L21(ProxOperator):
+    """pyproximal.L21(ndim, sigma): sum of pixel-wise 2-norms; dual prox = projection."""
+
+    def __init__(self, ndim, sigma=1.0):
+        super().__init__(None, False)
+        if int(ndim) != 2:
+            raise NotImplementedError("the CUDA path covers L21(ndim=2)")
+        self.ndim, self.sigma = int(ndim), sigma
+
+    def __call__(self, x):
+        v = _dev(x, (self.ndim, -1))
+        return float(self.sigma * v.pow(2).sum(dim=0).sqrt().sum().item())
+
+    def proxdual(self, x, tau):
+        v = _dev(x, (2, -1)).contiguous()
+        return imaging.proxdual(v, self.sigma, isotropic=True).cpu().numpy().reshape(np.shape(x))
+
+    def prox(self, x, tau):
+        x = np.asarray(x, dtype=np.float64)
+        return x - tau * self.proxdual(x / tau, 1.0 / tau)
+
+
+class TV(ProxOperator):
+    """pyproximal.TV(dims, sigma, niter, rtol): isotropic TV, prox by dual FISTA."""
+
+    def __init__(self, dims, sigma=1.0, niter=10, rtol=1e-4, **kwargs):
+        super().__init__(None, False)
+        self.dims = tuple(int(d) for d in dims)
+        if len(self.dims) != 2:
+            raise NotImplementedError("the CUDA path covers 2-D TV")
+        self.ndim, self.sigma, self.niter, self.rtol = 2, sigma, int(niter), rtol
+
+    def __call__(self, x):
+        g = imaging.grad(self.dims, _dev(x, (1, -1)))[0]
+        return float(self.sigma * g.pow(2).sum(dim=0).sqrt().sum().item())
+
+    def prox(self, x, tau):
+        x = np.asarray(x)
+        out = imaging.tv_prox(self.dims, _dev(x, (1, -1)), self.sigma * tau, self.niter, self.rtol)
+        return out.cpu().numpy().reshape(x.shape)
+
+
+class L2(ProxOperator):
+    """pyproximal.L2(Op, b, sigma, niter, warm): sigma/2 ||Op x - b||^2."""
+
+    def __init__(self, Op=None, b=None, q=None, sigma=1.0, alpha=1.0, qgrad=True, niter=10, x0=None,
+                 warm=True, densesolver=None, kwargs_solver=None):
+        super().__init__(Op, True)
+        if q is not None or alpha != 1.0 or densesolver is not None:
+            raise NotImplementedError("L2 with q / alpha / densesolver is not on the reference's path")
+        if Op is None or b is None:
+            raise NotImplementedError("the CUDA path covers L2 with an operator and data")
+        self.b, self.q, self.sigma, self.alpha, self.qgrad = b, q, sigma, alpha, qgrad
+        self.niter, self.x0, self.warm, self.count = int(niter), x0, warm, 0
+        self.kwargs_solver = {} if kwargs_solver is None else kwargs_solver
+        self._eng = None
+
+    def _engine(self):
+        if self._eng is None:
+            self._eng = imaging.DeconvEngine(self.Op.dims, self.Op.h, np.asarray(self.b), self.sigma, dtype="float64")
+        return self._eng
+
+    def __call__(self, x):
+        eng = self._engine()
+        r = imaging.blur(eng.spec, _dev(x, (1, -1))) - eng.b
+        return float(self.sigma / 2.0 * r.pow(2).sum().item())
+
+    def grad(self, x):
+        eng = self._engine()
+        r = imaging.blur(eng.spec, _dev(x, (1, -1))) - eng.b
+        return (self.sigma * imaging.blur(eng.spec, r, adjoint=True)).cpu().numpy().reshape(np.shape(x))
+
+    def prox(self, x, tau):
+        eng = self._engine()
+        torch = eng.torch
+        warm = _dev(self.x0, (1, -1)).clone() if (self.x0 is not None and self.warm) else \
+            torch.zeros((1, eng.P), dtype=torch.float64, device=eng.dev)
+        kw = self.kwargs_solver
+        out = eng.l2_prox(_dev(x, (1, -1)), tau, warm, iter_lim=self.niter, atol=kw.get("atol", 1e-6),
+                          btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8))
+        out = out.cpu().numpy().reshape(np.shape(x))
+        if self.warm:
+            self.x0 = out
+        return out

@@ -1,0 +1,133 @@
+"""Image-chain half of the benchmark (BASELINE.json configs[3], configs[4]):
+
+* MYULA deconvolution, 256x256, model M1 (L2(H5) + TV(sigma=0.3, niter=10, rtol=1e-4)),
+  tau=0.1125, gamma=0.5625 (prox_lmc_deconv.py:88-94, 465-473), a batch of independent chains
+  whose state is far larger than L2;
+* ULPDA deconvolution, 512x512, model M1 (L2(H5, niter=50, warm) + L21(0.3) + Gradient),
+  tau=0.534375, mu=1, theta=1, gfirst=False (prox_lmc_deconv.py:455-464).
+
+Synthetic data of the named shapes: a deterministic piecewise-smooth image in [0,255]
+(skimage's camera image is unavailable in this image), blurred by the CUDA H5
+operator plus N(0, 0.75^2) noise.  Nothing here imports oracle/.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import imaging, roofline
+
+SIGMA, TAU_REG = 0.75, 0.3
+
+
+def synthetic_image(ny, nx, seed=1234):
+    """Blocks, a disc, a ramp and a little texture, uint8-valued."""
+    yy, xx = np.mgrid[0:ny, 0:nx]
+    img = 40.0 + 60.0 * (xx / max(nx - 1, 1))
+    img[(yy > ny // 8) & (yy < ny // 2) & (xx > nx // 6) & (xx < nx // 2)] = 200.0
+    img[(yy - 0.65 * ny) ** 2 + (xx - 0.7 * nx) ** 2 < (0.18 * min(ny, nx)) ** 2] = 20.0
+    m = (yy > 0.6 * ny) & (xx < 0.4 * nx)
+    img[m] += 50.0 * np.sin(xx[m] * 0.35)
+    img += np.random.default_rng(seed).normal(0, 2.0, size=img.shape)
+    return np.clip(np.rint(img), 0, 255)
+
+
+def make_engine(dims, dev, dtype="float32", kernel=5, seed=0):
+    """Observation y = H5 img + N(0, sigma^2) (prox_lmc_deconv.py:53-59) and the engine for blur size k."""
+    import torch
+    img = synthetic_image(*dims)
+    h5 = imaging.pad_filter(np.ones((5, 5)) / 25.0, (2, 2))
+    x = torch.as_tensor(img.reshape(1, -1)).to(dev, torch.float64)
+    y = imaging.blur(imaging.BlurSpec(dims, h5), x)[0].cpu().numpy()
+    y = y + np.random.default_rng(seed).normal(0, SIGMA, size=y.shape)
+    hk = imaging.pad_filter(np.ones((kernel, kernel)) / kernel ** 2, (kernel // 2, kernel // 2))
+    return img, imaging.DeconvEngine(dims, hk, y, 1.0 / SIGMA ** 2, dtype=dtype, device=dev)
+
+
+def _time_launches(torch, dev, fn, steps, warmup):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize(dev)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        fn()
+    b.record()
+    torch.cuda.synchronize(dev)
+    return a.elapsed_time(b) * 1e-3 / steps
+
+
+def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dtype="float32"):
+    import torch
+    _, eng = make_engine(dims, dev, dtype)
+    L = 1.0 / SIGMA ** 2
+    gamma, tau = 1.0 / L, 0.2 / L
+    P = dims[0] * dims[1]
+    x = torch.zeros((chains, P), dtype=eng.tdt, device=dev)
+    mean = torch.zeros_like(x)
+    state = {"it": 0, "keep": None}
+
+    def launch():
+        state["keep"] = eng.myula(x, iters, tau, gamma, TAU_REG, 10, 1e-4, seed=0, mean=mean,
+                                  iter_offset=state["it"])
+        state["it"] += iters
+
+    for _ in range(2):      # burn-in so that the TV early exit is in its steady regime
+        launch()
+    torch.cuda.synchronize(dev)
+    eng.counters.zero_()
+    it0 = state["it"]
+    secs = _time_launches(torch, dev, launch, steps, warmup)
+    c = eng.read_counters()
+    n_it = state["it"] - it0
+    j = c["tv_sweeps"] / float(n_it * chains)
+    item = 4 if dtype == "float32" else 8
+    bpp = roofline.myula_bytes_per_pixel(j, item)
+    peaks = roofline.measured_peaks()
+    ach = bpp * P * chains * iters / secs / 1e9
+    return {"metric": "myula_deconv_chain_iters_per_sec", "value": chains * iters / secs, "unit": "chain-iters/s",
+            "pixel_iters_per_sec": chains * iters * P / secs, "dtype": dtype, "dims": list(dims), "chains": chains,
+            "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "tv_sweeps_per_iter": j,
+            "state_bytes": int(10 * chains * P * item), "l2_policy": "per-chain arrays total far more than the 126 MB L2",
+            "roofline": {"bound": "hbm", "kernel": "img_myula_kernel<%s>" % ("float" if item == 4 else "double"),
+                         "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
+                         "bytes_per_pixel_iter": bpp, "traffic": None, "peak_source": peaks["source"]}}
+
+
+def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtype="float32"):
+    import torch
+    _, eng = make_engine(dims, dev, dtype)
+    L = 1.0 / SIGMA ** 2
+    tau, mu = 0.95 / L, 1.0
+    P = dims[0] * dims[1]
+    z = lambda *s: torch.zeros(s, dtype=eng.tdt, device=dev)
+    x, xhat, y, warm, mean = z(chains, P), z(chains, P), z(chains, 2, P), z(chains, P), z(chains, P)
+    state = {"it": 0, "keep": None}
+
+    def launch():
+        state["keep"] = eng.ulpda(x, xhat, y, warm, iters, tau, mu, 1.0, TAU_REG, True, False, 50, seed=0,
+                                  mean=mean, iter_offset=state["it"])
+        state["it"] += iters
+
+    for _ in range(3):
+        launch()
+    torch.cuda.synchronize(dev)
+    eng.counters.zero_()
+    secs = _time_launches(torch, dev, launch, steps, warmup)
+    c = eng.read_counters()
+    k = c["lsqr_iterations"] / max(1.0, float(c["lsqr_solves"]))
+    item = 4 if dtype == "float32" else 8
+    bpp = roofline.ulpda_bytes_per_pixel(k, item)
+    peaks = roofline.measured_peaks()
+    ach = bpp * P * chains * iters / secs / 1e9
+    return {"metric": "ulpda_deconv_chain_iters_per_sec", "value": chains * iters / secs, "unit": "chain-iters/s",
+            "pixel_iters_per_sec": chains * iters * P / secs, "dtype": dtype, "dims": list(dims), "chains": chains,
+            "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "lsqr_iters_per_solve": k,
+            "roofline": {"bound": "hbm", "kernel": "img_ulpda_kernel<%s>" % ("float" if item == 4 else "double"),
+                         "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
+                         "bytes_per_pixel_iter": bpp, "traffic": None, "peak_source": peaks["source"]}}
+
+
+def run(dev, steps=3, warmup=3, **kw):
+    out = run_myula(dev, steps=steps, warmup=warmup, **kw)
+    out["ulpda"] = run_ulpda(dev, steps=max(1, min(steps, 3)), warmup=min(warmup, 2))
+    return out

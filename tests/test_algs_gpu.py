@@ -1,0 +1,109 @@
+"""Drop-in ``algs`` surface (algs.py:295-587) against the oracle, called the way
+prox_lmc_deconv.py:455-473 calls it: operator objects in, (niter, P) float64 samples out,
+seed-driven noise, per-iteration callback with a host array."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(b).max(), 1e-300)
+
+
+def _setup(dims, k=5):
+    from oracle import deconv_ref as D
+    from lmc_atomi_b200 import compat
+    pb = D.build_problem(D.synthetic_image(*dims), kernel=k)
+    hk = np.ones((k, k)) / k ** 2
+    H = compat.Convolve2D(dims, h=hk, offset=(k // 2, k // 2))
+    l2 = compat.L2(Op=H, b=pb["y"].ravel(), sigma=1 / 0.75 ** 2, niter=50, warm=True)
+    return D, compat, pb, H, l2
+
+
+@pytest.mark.parametrize("dims,k", [((48, 40), 5), ((37, 61), 6)])
+def test_myula_dropin_matches_oracle_with_callback(dims, k):
+    from lmc_atomi_b200 import algs
+    D, compat, pb, H, l2 = _setup(dims, k)
+    N = 12
+    seen_ref, seen = [], []
+    want = D.MoreauYosidaUnadjustedLangevin(pb["l2"](), pb["tv"](), pb["x0"], tau=pb["tau_myula"],
+                                            gamma=pb["gamma_myula"], niter=N, seed=3,
+                                            callback=lambda x: seen_ref.append(x.copy()))
+    tv = compat.TV(dims, sigma=0.3, niter=10)
+    got = algs.MoreauYosidaUnadjustedLangevin(l2, tv, pb["x0"], tau=pb["tau_myula"], gamma=pb["gamma_myula"],
+                                              niter=N, seed=3, callback=lambda x: seen.append(x.copy()))
+    assert got.shape == want.shape == (N, dims[0] * dims[1]) and got.dtype == np.float64
+    assert rel(got, want) < 1e-11
+    assert len(seen) == N and rel(np.array(seen), np.array(seen_ref)) < 1e-11
+    # no callback: one launch for all iterations, same samples
+    got2 = algs.MoreauYosidaUnadjustedLangevin(l2, tv, pb["x0"], tau=pb["tau_myula"], gamma=pb["gamma_myula"],
+                                               niter=N, seed=3)
+    assert rel(got2, got) < 1e-13
+
+
+@pytest.mark.parametrize("iso,gfirst", [(True, False), (False, False), (True, True)])
+def test_ulpda_dropin_matches_oracle(iso, gfirst):
+    from lmc_atomi_b200 import algs
+    dims, N = (48, 40), 8
+    D, compat, pb, H, l2 = _setup(dims)
+    g_ref = pb["l1iso"]() if iso else pb["l1"]()
+    want, wy = D.UnadjustedLangevinPrimalDual(pb["l2"](), g_ref, pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"],
+                                              theta=1., niter=N, seed=1, gfirst=gfirst, returny=True)
+    g = compat.L21(ndim=2, sigma=0.3) if iso else compat.L1(sigma=0.3)
+    seen = []
+    got, gy = algs.UnadjustedLangevinPrimalDual(l2, g, compat.Gradient(dims), pb["x0"], tau=pb["tau0"],
+                                                mu=pb["mu0"], theta=1., niter=N, seed=1, gfirst=gfirst,
+                                                returny=True, callback=lambda x: seen.append(x.copy()))
+    assert got.shape == (N, dims[0] * dims[1]) and gy.shape == (N, 2 * dims[0] * dims[1])
+    assert rel(got, want) < 1e-10 and rel(gy, wy) < 1e-10
+    assert len(seen) == N and rel(np.array(seen), want) < 1e-10
+    assert l2.x0 is not None and l2.x0.shape == (dims[0] * dims[1],)   # warm start kept, like pyproximal.L2
+
+
+def test_ulpda_variable_steps_and_z():
+    from lmc_atomi_b200 import algs
+    dims, N = (40, 44), 6
+    D, compat, pb, H, l2 = _setup(dims)
+    taus = pb["tau0"] * np.linspace(1.0, 0.5, N)
+    mus = np.linspace(1.0, 0.8, N)
+    z = np.random.default_rng(5).normal(0, 0.1, dims[0] * dims[1])
+    want = D.UnadjustedLangevinPrimalDual(pb["l2"](), pb["l1iso"](), pb["Gop"], pb["x0"], taus, mus, z=z,
+                                          theta=0.7, niter=N, seed=2, gfirst=False)
+    got = algs.UnadjustedLangevinPrimalDual(l2, compat.L21(ndim=2, sigma=0.3), compat.Gradient(dims), pb["x0"],
+                                            tau=taus, mu=mus, z=z, theta=0.7, niter=N, seed=2, gfirst=False)
+    assert rel(got, want) < 1e-10
+
+
+def test_compat_operators_match_oracle():
+    dims = (37, 61)
+    D, compat, pb, H, l2 = _setup(dims, 6)
+    rng = np.random.default_rng(0)
+    x = rng.normal(size=dims[0] * dims[1]) * 50
+    l2r, tvr, gr = pb["l2"](), pb["tv"](), pb["Gop"]
+    assert rel(H.matvec(x), pb["H"].matvec(x)) < 1e-13 and rel(H.rmatvec(x), pb["H"].rmatvec(x)) < 1e-13
+    assert rel(H.H * x, pb["H"].rmatvec(x)) < 1e-13
+    assert abs(l2(x) - l2r(x)) / l2r(x) < 1e-12
+    assert rel(l2.grad(x), l2r.grad(x)) < 1e-12
+    G = compat.Gradient(dims)
+    assert rel(G.matvec(x), gr.matvec(x)) < 1e-14
+    v = rng.normal(size=2 * dims[0] * dims[1])
+    assert rel(G.rmatvec(v), gr.rmatvec(v)) < 1e-14
+    tv = compat.TV(dims, sigma=0.3, niter=10)
+    assert abs(tv(x) - tvr(x)) / tvr(x) < 1e-12
+    assert rel(tv.prox(x, 0.5625), tvr.prox(x, 0.5625)) < 1e-12
+    for mine, ref in ((compat.L21(2, 0.3), pb["l1iso"]()), (compat.L1(0.3), pb["l1"]())):
+        assert abs(mine(v) - ref(v)) / ref(v) < 1e-12
+        assert rel(mine.proxdual(v, 1.0), ref.proxdual(v, 1.0)) < 1e-14
+        assert rel(mine.prox(v, 0.7), ref.prox(v, 0.7)) < 1e-13
+    assert rel(l2.prox(x, 0.53), l2r.prox(x.copy(), 0.53)) < 1e-10
+
+
+def test_unsupported_combination_raises():
+    from lmc_atomi_b200 import algs
+    dims = (32, 32)
+    D, compat, pb, H, l2 = _setup(dims)
+    with pytest.raises(NotImplementedError):
+        algs.MoreauYosidaUnadjustedLangevin(l2, compat.L1(0.3), pb["x0"], tau=0.1, gamma=0.5, niter=2)
+    with pytest.raises(NotImplementedError):
+        algs.UnadjustedLangevinPrimalDual(l2, compat.TV(dims), compat.Gradient(dims), pb["x0"], 0.5, 1.0, niter=2)
