@@ -54,6 +54,45 @@ __host__ __device__ __forceinline__ uint4 lmc_philox4x32_10(uint4 ctr, uint2 key
   return ctr;
 }
 
+// Same generator with the ten round keys precomputed (host side / once per kernel): per
+// round two 32x32->64 multiplies (IMAD.WIDE) and two three-input XORs whose key operand is
+// a constant-bank word.
+__host__ __device__ __forceinline__ void lmc_philox_round_keys(uint2 key, uint32_t rk[20]) {
+  for (int r = 0; r < 10; ++r) {
+    rk[2 * r] = key.x + (uint32_t)r * LMC_PHILOX_W0;
+    rk[2 * r + 1] = key.y + (uint32_t)r * LMC_PHILOX_W1;
+  }
+}
+
+__device__ __forceinline__ uint4 lmc_philox4x32_10_rk(uint4 ctr, const uint32_t* __restrict__ rk) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const unsigned long long p0 = (unsigned long long)LMC_PHILOX_M0 * ctr.x;
+    const unsigned long long p1 = (unsigned long long)LMC_PHILOX_M1 * ctr.z;
+    ctr = make_uint4((uint32_t)(p1 >> 32) ^ ctr.y ^ rk[2 * r], (uint32_t)p1,
+                     (uint32_t)(p0 >> 32) ^ ctr.w ^ rk[2 * r + 1], (uint32_t)p0);
+  }
+  return ctr;
+}
+
+// ------------------------------------------------------------------ MUFU-backed fp32 primitives
+// One SFU instruction each (relative error about 2^-22), no slow paths: the register-resident
+// chains are bound by instruction issue, so the libdevice range-reduction sequences matter.
+#define LMC_MUFU1(name, op)                                            \
+  __device__ __forceinline__ float name(float x) {                     \
+    float y;                                                           \
+    asm(op " %0, %1;" : "=f"(y) : "f"(x));                             \
+    return y;                                                          \
+  }
+LMC_MUFU1(lmc_ex2f, "ex2.approx.ftz.f32")
+LMC_MUFU1(lmc_lg2f, "lg2.approx.ftz.f32")
+LMC_MUFU1(lmc_rcpf, "rcp.approx.ftz.f32")
+LMC_MUFU1(lmc_sqrtf, "sqrt.approx.ftz.f32")
+LMC_MUFU1(lmc_rsqrtf, "rsqrt.approx.ftz.f32")
+LMC_MUFU1(lmc_sinf, "sin.approx.ftz.f32")
+LMC_MUFU1(lmc_cosf, "cos.approx.ftz.f32")
+#undef LMC_MUFU1
+
 // streams of one chain (second counter word)
 #define LMC_STREAM_STEP 0u
 #define LMC_STREAM_INIT 1u
@@ -63,29 +102,39 @@ template <typename T> struct Math;
 
 template <> struct Math<float> {
   static constexpr bool is_double = false;
-  __device__ __forceinline__ static float exp2(float x) { return exp2f(x); }
-  __device__ __forceinline__ static float log2(float x) { return __log2f(x); }
-  __device__ __forceinline__ static float exp(float x) { return __expf(x); }
-  __device__ __forceinline__ static float sqrt(float x) { return sqrtf(x); }
-  __device__ __forceinline__ static float rsqrt(float x) { return rsqrtf(x); }
-  __device__ __forceinline__ static float rcp(float x) { return __frcp_rn(x); }
-  __device__ __forceinline__ static float div(float a, float b) { return __fdividef(a, b); }
-  __device__ __forceinline__ static float sinh(float x) { return sinhf(x); }
-  __device__ __forceinline__ static float asinh(float x) { return asinhf(x); }
+  __device__ __forceinline__ static float exp2(float x) { return lmc_ex2f(x); }
+  __device__ __forceinline__ static float log2(float x) { return lmc_lg2f(x); }
+  __device__ __forceinline__ static float exp(float x) { return lmc_ex2f(x * 1.4426950408889634f); }
+  __device__ __forceinline__ static float log(float x) { return lmc_lg2f(x) * 0.6931471805599453f; }
+  __device__ __forceinline__ static float sqrt(float x) { return lmc_sqrtf(x); }
+  __device__ __forceinline__ static float rsqrt(float x) { return lmc_rsqrtf(x); }
+  __device__ __forceinline__ static float rcp(float x) { return lmc_rcpf(x); }
+  __device__ __forceinline__ static float div(float a, float b) { return a * lmc_rcpf(b); }
+  // sinh(x) = (2^(x log2 e) - 2^(-x log2 e)) / 2; absolute error ~1e-7 cosh(x)
+  __device__ __forceinline__ static float sinh(float x) {
+    float a = x * 1.4426950408889634f;
+    return 0.5f * (lmc_ex2f(a) - lmc_ex2f(-a));
+  }
+  // asinh(x) = sign(x) ln(|x| + sqrt(x^2 + 1))
+  __device__ __forceinline__ static float asinh(float x) {
+    float ax = fabsf(x);
+    float l = lmc_lg2f(ax + lmc_sqrtf(fmaf(ax, ax, 1.0f))) * 0.6931471805599453f;
+    return copysignf(l, x);
+  }
   __device__ __forceinline__ static float abs(float x) { return fabsf(x); }
   __device__ __forceinline__ static float max(float a, float b) { return fmaxf(a, b); }
   __device__ __forceinline__ static float min(float a, float b) { return fminf(a, b); }
   __device__ __forceinline__ static float fma(float a, float b, float c) { return fmaf(a, b, c); }
   __device__ __forceinline__ static float floor(float a) { return floorf(a); }
-  // two N(0,1) from two 32-bit words (Box-Muller); u1 in (0,1], 24-bit resolution
+  // two N(0,1) from two 32-bit words (Box-Muller) on the top 24 bits of each word:
+  // u1 = (a24 + 1) 2^-24 in (0,1]; angle = 2 pi b24 2^-24 taken in [-pi, pi) (b24 read as a
+  // signed 24-bit number: same cos/sin by periodicity, better conditioned for MUFU.SIN/COS).
   __device__ __forceinline__ static void normals(uint32_t a, uint32_t b, float& z0, float& z1) {
-    float u1 = ((float)(a >> 8) + 1.0f) * 5.9604644775390625e-8f;  // 2^-24
-    float u2 = (float)(b >> 8) * 5.9604644775390625e-8f;
-    float r = sqrtf(-2.0f * __logf(u1));
-    float s, c;
-    sincospif(2.0f * u2, &s, &c);
-    z0 = r * c;
-    z1 = r * s;
+    float u1 = fmaf((float)(a >> 8), 5.9604644775390625e-8f, 5.9604644775390625e-8f);
+    float ang = (float)((int32_t)b >> 8) * 3.7450703661175736e-7f;   // 2 pi 2^-24
+    float r = lmc_sqrtf(lmc_lg2f(u1) * -1.3862943611198906f);        // sqrt(-2 ln u1)
+    z0 = r * lmc_cosf(ang);
+    z1 = r * lmc_sinf(ang);
   }
   __device__ __forceinline__ static float uniform(uint32_t a) {
     return (float)(a >> 8) * 5.9604644775390625e-8f;  // [0,1)
@@ -97,6 +146,7 @@ template <> struct Math<double> {
   __device__ __forceinline__ static double exp2(double x) { return ::exp2(x); }
   __device__ __forceinline__ static double log2(double x) { return ::log2(x); }
   __device__ __forceinline__ static double exp(double x) { return ::exp(x); }
+  __device__ __forceinline__ static double log(double x) { return ::log(x); }
   __device__ __forceinline__ static double sqrt(double x) { return ::sqrt(x); }
   __device__ __forceinline__ static double rsqrt(double x) { return 1.0 / ::sqrt(x); }
   __device__ __forceinline__ static double rcp(double x) { return 1.0 / x; }

@@ -28,6 +28,8 @@ struct MixP {
   real lc[NMAX];    // log2 of the component's constant factor (omega_i / norm_i or omega_i (alpha_i/2)^2)
   real al[NMAX];    // Laplacian scale alpha_i
   real thr[NMAX];   // lamda * alpha_i
+  real c1[NMAX];    // -log2(e) alpha_i
+  real c2;          // -log2(e) / (2 lamda)
   real lamda, inv_lamda;
   // l1 prior (GAUSS_L1)
   real pr_alpha, pr_thr, pr_mu0, pr_mu1;
@@ -39,6 +41,7 @@ struct MixP {
   real qi00, qi01, qi10, qi11;  // Q^-1
   real eta, inv_eta, pp_thr;    // PPULA dual step, 1/eta, lamda/eta
   real b0, b1, sg0, sg1;        // beta, sigma
+  real ib0, ib1, isg0, isg1;    // their reciprocals
   real hshift;
 };
 
@@ -55,6 +58,7 @@ struct MixIo {
   long long C, K, burnin, hist_every;
   unsigned long long chain_offset;
   uint2 key;
+  uint32_t rk[20];       // Philox round keys (host-computed from key)
   int init_from_rng, hist_bins;
   double hist_lo, hist_scale;  // bin = floor((x - lo) * scale)
   int n_items;
@@ -115,51 +119,50 @@ __device__ __forceinline__ void eval_gauss(const MixP<real>& P, real t0, real t1
   }
 }
 
-// Moreau-smoothed Laplacian mixture: lmc_laplace.py:43-92.
+// Moreau-smoothed Laplacian mixture: lmc_laplace.py:43-92.  With d = theta - mu_i and
+// r = clamp(d, -lamda alpha_i, lamda alpha_i) = theta - prox (lmc_laplace.py:53-54), s = d - r = prox - mu_i:
+// envelope = alpha_i |s|_1 + |r|^2 / (2 lamda) (56-58), component gradient direction r / lamda (70-71).
 template <typename real, int NC, bool HESS>
 __device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real t1, Eval<real>& e) {
   using M = Math<real>;
   const int n = NC > 0 ? NC : P.n;
-  real a[NMAX], v0[NMAX], v1[NMAX];
+  real a[NMAX], r0[NMAX], r1[NMAX];
   real amax = real(-1e30);
-  const real l2e = real(1.4426950408889634);
 #pragma unroll
   for (int i = 0; i < NMAX; ++i) {
     if (i < n) {
       real d0 = t0 - P.mu0[i], d1 = t1 - P.mu1[i];
-      real s0 = lmc_soft(d0, P.thr[i]), s1 = lmc_soft(d1, P.thr[i]);  // prox - mu  (lmc_laplace.py:53-54)
-      real r0 = d0 - s0, r1 = d1 - s1;                               // theta - prox
-      // Moreau envelope (lmc_laplace.py:56-58)
-      real env = M::fma(P.al[i], M::abs(s0) + M::abs(s1),
-                        M::fma(r0, r0, r1 * r1) * (real(0.5) * P.inv_lamda));
-      a[i] = M::fma(env, -l2e, P.lc[i]);
-      v0[i] = r0 * P.inv_lamda;  // (theta - prox)/lamda = -grad of the component / pdf
-      v1[i] = r1 * P.inv_lamda;
+      r0[i] = M::max(M::min(d0, P.thr[i]), -P.thr[i]);
+      r1[i] = M::max(M::min(d1, P.thr[i]), -P.thr[i]);
+      real s1n = M::abs(d0 - r0[i]) + M::abs(d1 - r1[i]);
+      real rr = M::fma(r0[i], r0[i], r1[i] * r1[i]);
+      a[i] = M::fma(rr, P.c2, M::fma(s1n, P.c1[i], P.lc[i]));   // log2(omega_i pdf_lamda,i)
       amax = M::max(amax, a[i]);
     }
   }
   real S = 0, gp0 = 0, gp1 = 0, hp00 = 0, hp01 = 0, hp11 = 0;
-  real l1 = M::abs(t0) + M::abs(t1);
+  const real l1 = M::abs(t0) + M::abs(t1);
 #pragma unroll
   for (int i = 0; i < NMAX; ++i) {
     if (i < n) {
       real w = M::exp2(a[i] - amax);
       S += w;
-      gp0 = M::fma(w, v0[i], gp0);
-      gp1 = M::fma(w, v1[i], gp1);
+      gp0 = M::fma(w, r0[i], gp0);
+      gp1 = M::fma(w, r1[i], gp1);
       if (HESS) {
         // lmc_laplace.py:80-82 (sic): weight (alpha/2)^2 exp(-alpha ||theta||_1), no mu,
-        // unsmoothed exponent; matrix (-I + g g^T).
-        real wq = M::exp2(M::fma(P.al[i] * l1, -l2e, P.lc[i]) - amax);
-        hp00 = M::fma(wq, M::fma(v0[i], v0[i], real(-1)), hp00);
-        hp01 = M::fma(wq, v0[i] * v1[i], hp01);
-        hp11 = M::fma(wq, M::fma(v1[i], v1[i], real(-1)), hp11);
+        // unsmoothed exponent; matrix (-I + g g^T) with g = r / lamda.
+        real v0 = r0[i] * P.inv_lamda, v1 = r1[i] * P.inv_lamda;
+        real wq = M::exp2(M::fma(l1, P.c1[i], P.lc[i]) - amax);
+        hp00 = M::fma(wq, M::fma(v0, v0, real(-1)), hp00);
+        hp01 = M::fma(wq, v0 * v1, hp01);
+        hp11 = M::fma(wq, M::fma(v1, v1, real(-1)), hp11);
       }
     }
   }
-  real rS = M::rcp(S);
-  e.g0 = gp0 * rS;
-  e.g1 = gp1 * rS;
+  const real rS = M::rcp(S), gS = rS * P.inv_lamda;
+  e.g0 = gp0 * gS;
+  e.g1 = gp1 * gS;
   e.logp2 = amax + M::log2(S);
   if (HESS) {
     e.h00 = M::fma(e.g0, e.g0, -hp00 * rS);
@@ -180,12 +183,19 @@ __device__ __forceinline__ void spd_inv_sqrt(real a, real b, real d, real& i00, 
                                              real& r00, real& r01, real& r11) {
   using M = Math<real>;
   real det = M::fma(a, d, -b * b);
-  real rdet = real(1) / det;
+  real rdet = M::rcp(det);
   i00 = d * rdet; i01 = -b * rdet; i11 = a * rdet;          // M = H^-1
   real sdet = M::sqrt(M::fma(i00, i11, -i01 * i01));        // sqrt(det M)
   real tr = i00 + i11;
-  real rs = real(1) / M::sqrt(tr + real(2) * sdet);
+  real rs = M::rsqrt(tr + real(2) * sdet);
   r00 = (i00 + sdet) * rs; r01 = i01 * rs; r11 = (i11 + sdet) * rs;  // sqrtm(M)
+}
+
+// asinh(t / b) from sq = sqrt(t^2 + b^2) and ib = 1 / b
+template <typename real>
+__device__ __forceinline__ real mirror_asinh(real t, real sq, real ib) {
+  using M = Math<real>;
+  return copysign(M::log((M::abs(t) + sq) * ib), t);
 }
 
 template <int ALG> struct AlgTraits {
@@ -263,33 +273,35 @@ __device__ __forceinline__ void step_unadjusted(const MixP<real>& P, real& t0, r
     t0 = M::fma(P.s2g, z0, M::fma(-P.gamma, n0, t0));
     t1 = M::fma(P.s2g, z1, M::fma(-P.gamma, n1, t1));
   } else if (ALG == LMC_MLA || ALG == LMC_LBMUMLA) {
-    // lmc.py:186-187 / prox_lmc.py:251-252: mirror map grad = asinh(theta/beta)
-    real q0 = M::fma(t0, t0, P.b0 * P.b0), q1 = M::fma(t1, t1, P.b1 * P.b1);
-    real e0 = M::asinh(t0 / P.b0) - P.gamma * e.g0;
-    real e1 = M::asinh(t1 / P.b1) - P.gamma * e.g1;
+    // lmc.py:186-187 / prox_lmc.py:251-252: mirror map grad = asinh(theta/beta), evaluated as
+    // sign(theta) log((|theta| + sqrt(theta^2 + beta^2)) / beta): the root is shared with the
+    // noise scale (theta^2 + beta^2)^(-1/4).
+    real sq0 = M::sqrt(M::fma(t0, t0, P.b0 * P.b0)), sq1 = M::sqrt(M::fma(t1, t1, P.b1 * P.b1));
+    real e0 = mirror_asinh(t0, sq0, P.ib0) - P.gamma * e.g0;
+    real e1 = mirror_asinh(t1, sq1, P.ib1) - P.gamma * e.g1;
     if (ALG == LMC_LBMUMLA) {
       // prox_lmc.py:218-242 with beta := sigma (the reference passes sigma there)
       real thr = P.pr_thr;
       real sh = M::sinh(thr);
       {
-        real as = M::asinh(t0 / P.sg0);
-        real lo = P.sg0 * M::sinh(as - thr), hi = P.sg0 * M::sinh(as + thr);
         real rt = M::sqrt(M::fma(t0, t0, P.sg0 * P.sg0));
+        real as = mirror_asinh(t0, rt, P.isg0);
+        real lo = P.sg0 * M::sinh(as - thr), hi = P.sg0 * M::sinh(as + thr);
         real p = (t0 > P.sg0 * sh) ? lo : (rt - P.sg0);
         p = (t0 < -P.sg0 * sh) ? hi : p;
-        e0 -= P.gamma * (P.inv_lamda / rt * (t0 - p));
+        e0 -= P.gamma * (M::div(P.inv_lamda, rt) * (t0 - p));
       }
       {
-        real as = M::asinh(t1 / P.sg1);
-        real lo = P.sg1 * M::sinh(as - thr), hi = P.sg1 * M::sinh(as + thr);
         real rt = M::sqrt(M::fma(t1, t1, P.sg1 * P.sg1));
+        real as = mirror_asinh(t1, rt, P.isg1);
+        real lo = P.sg1 * M::sinh(as - thr), hi = P.sg1 * M::sinh(as + thr);
         real p = (t1 > P.sg1 * sh) ? lo : (rt - P.sg1);
         p = (t1 < -P.sg1 * sh) ? hi : p;
-        e1 -= P.gamma * (P.inv_lamda / rt * (t1 - p));
+        e1 -= P.gamma * (M::div(P.inv_lamda, rt) * (t1 - p));
       }
     }
-    e0 = M::fma(P.s2g * M::rsqrt(M::sqrt(q0)), x0, e0);
-    e1 = M::fma(P.s2g * M::rsqrt(M::sqrt(q1)), x1, e1);
+    e0 = M::fma(P.s2g * M::rsqrt(sq0), x0, e0);
+    e1 = M::fma(P.s2g * M::rsqrt(sq1), x1, e1);
     t0 = P.b0 * M::sinh(e0);
     t1 = P.b1 * M::sinh(e1);
   } else if (ALG == LMC_FBULA) {
@@ -313,16 +325,170 @@ __device__ __forceinline__ real mh_logdens2(const MixP<real>& P, real t0, real t
   return l;
 }
 
+// State of one chain (registers of one thread) + the per-step arithmetic shared by the
+// validation loop (host-supplied noise, trajectory written every step) and the production
+// loop (Philox noise, nothing but registers touched inside the K-loop).
 template <typename real, int TARGET, int ALG, int NC>
+struct Chain {
+  using M = Math<real>;
+  static constexpr bool ADJ = AlgTraits<ALG>::adjusted;
+  real t0, t1;
+  real cc0, cc1, clog;   // MH chains: proposal centre and log2-density at the current state
+  uint32_t nacc;
+  real b_n, b_s0, b_s1, b_s00, b_s01, b_s11;        // fp32/fp64 partial sums of <= 32 steps
+  double m_n, m_s0, m_s1, m_s00, m_s01, m_s11;      // fp64 totals
+
+  __device__ __forceinline__ void init(const MixP<real>& P, real a0, real a1) {
+    t0 = a0; t1 = a1;
+    cc0 = cc1 = clog = 0;
+    nacc = 0;
+    b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = 0;
+    m_n = m_s0 = m_s1 = m_s00 = m_s01 = m_s11 = 0;
+    if (ADJ) {
+      Eval<real> cur;
+      eval_target<real, TARGET, NC, false>(P, t0, t1, cur);
+      drift_centre<real, ALG>(P, t0, t1, cur, cc0, cc1);
+      clog = mh_logdens2<real, ALG>(P, t0, t1, cur);
+    }
+  }
+
+  // one transition; returns whether a sample was emitted (always, for unadjusted samplers)
+  __device__ __forceinline__ bool step(const MixP<real>& P, real x0, real x1, real u) {
+    if (!ADJ) {
+      step_unadjusted<real, TARGET, ALG, NC>(P, t0, t1, x0, x1);
+      return true;
+    }
+    // lmc.py:124-130: propose, MH ratio p(new) q(old|new) / (p(old) q(new|old)),
+    // accept iff u <= min(1, ratio); a NaN ratio accepts (Python's min(1, nan) == 1).
+    real n0 = M::fma(P.s2g, x0, cc0), n1 = M::fma(P.s2g, x1, cc1);
+    Eval<real> prop;
+    eval_target<real, TARGET, NC, false>(P, n0, n1, prop);
+    real pc0, pc1;
+    drift_centre<real, ALG>(P, n0, n1, prop, pc0, pc1);
+    real plog = mh_logdens2<real, ALG>(P, n0, n1, prop);
+    real f0 = t0 - pc0, f1 = t1 - pc1;   // old | new
+    real r0 = n0 - cc0, r1 = n1 - cc1;   // new | old
+    real lq = (M::fma(r0, r0, r1 * r1) - M::fma(f0, f0, f1 * f1)) * P.inv4g;  // natural log
+    real lr2 = (plog - clog) + real(1.4426950408889634) * lq;
+    real ratio = M::exp2(lr2);
+    bool emitted = !(u > M::min(real(1), ratio));
+    if (emitted) {
+      t0 = n0; t1 = n1; cc0 = pc0; cc1 = pc1; clog = plog;
+      ++nacc;
+    }
+    return emitted;
+  }
+
+  // running sums over the emitted samples
+  __device__ __forceinline__ void accumulate(bool emitted) {
+    if (ADJ) {
+      real f = emitted ? real(1) : real(0);
+      b_n += f;
+      b_s0 = M::fma(f, t0, b_s0);
+      b_s1 = M::fma(f, t1, b_s1);
+      b_s00 = M::fma(f * t0, t0, b_s00);
+      b_s01 = M::fma(f * t0, t1, b_s01);
+      b_s11 = M::fma(f * t1, t1, b_s11);
+    } else {
+      b_s0 += t0;
+      b_s1 += t1;
+      b_s00 = M::fma(t0, t0, b_s00);
+      b_s01 = M::fma(t0, t1, b_s01);
+      b_s11 = M::fma(t1, t1, b_s11);
+    }
+  }
+
+  __device__ __forceinline__ void flush() {
+    m_n += b_n; m_s0 += b_s0; m_s1 += b_s1; m_s00 += b_s00; m_s01 += b_s01; m_s11 += b_s11;
+    b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = 0;
+  }
+};
+
+__device__ __forceinline__ void hist_add(const MixIo& io, double a0, double a1) {
+  int ix = (int)floor((a0 - io.hist_lo) * io.hist_scale);
+  int iy = (int)floor((a1 - io.hist_lo) * io.hist_scale);
+  if (ix >= 0 && ix < io.hist_bins && iy >= 0 && iy < io.hist_bins)
+    atomicAdd(&io.hist[ix * io.hist_bins + iy], 1ull);
+}
+
+// Production loop over steps [kb, ke): Philox noise, registers only.  STATS = accumulate
+// moments (steps past the burn-in), HIST = bin every io.hist_every-th emitted step.
+// Unadjusted samplers use one Philox block per TWO steps (words x,y for even k, z,w for odd
+// k, block counter k >> 1); adjusted samplers one block per step (x,y normals, z uniform).
+template <typename real, int TARGET, int ALG, int NC, bool STATS, bool HIST>
+__device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch, const MixP<real>& P,
+                                               const MixIo& io, uint32_t c_lo, uint32_t c_hi, bool live,
+                                               long long kb, long long ke) {
+  using M = Math<real>;
+  constexpr bool ADJ = AlgTraits<ALG>::adjusted;
+  long long hcount = 0;
+  if (HIST) hcount = io.hist_every - (kb % io.hist_every);
+  auto after = [&](bool emitted) {
+    if (STATS) ch.accumulate(emitted);
+    if (HIST) {
+      if (--hcount == 0) {
+        hcount = io.hist_every;
+        if (emitted && live) hist_add(io, (double)ch.t0, (double)ch.t1);
+      }
+    }
+  };
+  auto block = [&](long long ctr) {
+    return lmc_philox4x32_10_rk(make_uint4((uint32_t)ctr, LMC_STREAM_STEP | ((uint32_t)(ctr >> 32) << 8), c_lo, c_hi),
+                                io.rk);
+  };
+  long long k = kb;
+  if (ADJ) {
+    while (k < ke) {
+      const int n = (int)((ke - k) < 32 ? (ke - k) : 32);
+      for (int j = 0; j < n; ++j) {
+        uint4 r = block(k + j);
+        real x0, x1;
+        M::normals(r.x, r.y, x0, x1);
+        after(ch.step(P, x0, x1, M::uniform(r.z)));
+      }
+      if (STATS) ch.flush();
+      k += n;
+    }
+    return;
+  }
+  if ((k & 1) && k < ke) {   // odd start (odd burn-in): second half of block k >> 1
+    uint4 r = block(k >> 1);
+    real x0, x1;
+    M::normals(r.z, r.w, x0, x1);
+    after(ch.step(P, x0, x1, real(0)));
+    ++k;
+  }
+  while (k + 1 < ke) {
+    const long long left = (ke - k) >> 1;
+    const int n = (int)(left < 16 ? left : 16);
+    const long long c0 = k >> 1;
+    for (int j = 0; j < n; ++j) {
+      uint4 r = block(c0 + j);
+      real x0, x1;
+      M::normals(r.x, r.y, x0, x1);
+      after(ch.step(P, x0, x1, real(0)));
+      M::normals(r.z, r.w, x0, x1);
+      after(ch.step(P, x0, x1, real(0)));
+    }
+    if (STATS) ch.flush();
+    k += 2 * n;
+  }
+  if (k < ke) {
+    uint4 r = block(k >> 1);
+    real x0, x1;
+    M::normals(r.x, r.y, x0, x1);
+    after(ch.step(P, x0, x1, real(0)));
+  }
+  if (STATS) ch.flush();
+}
+
+template <typename real, int TARGET, int ALG, int NC, bool PROD>
 __global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant__ MixP<real> P,
                                                           const __grid_constant__ MixIo io) {
   using M = Math<real>;
   constexpr bool ADJ = AlgTraits<ALG>::adjusted;
   const int lane = threadIdx.x & 31;
   real* theta = (real*)io.theta;
-  const real* noise = (const real*)io.noise;
-  const real* unif = (const real*)io.unif;
-  real* traj = (real*)io.traj;
   const long long K = io.K;
 
   for (;;) {
@@ -335,114 +501,70 @@ __global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant_
     const unsigned long long gc = io.chain_offset + (unsigned long long)(live ? c : 0);
     const uint32_t c_lo = (uint32_t)gc, c_hi = (uint32_t)(gc >> 32);
 
-    real t0 = 0, t1 = 0;
+    real a0 = 0, a1 = 0;
     if (io.init_from_rng) {
-      uint4 r = lmc_philox4x32_10(make_uint4(0u, LMC_STREAM_INIT, c_lo, c_hi), io.key);
-      M::normals(r.x, r.y, t0, t1);
+      uint4 r = lmc_philox4x32_10_rk(make_uint4(0u, LMC_STREAM_INIT, c_lo, c_hi), io.rk);
+      M::normals(r.x, r.y, a0, a1);
     } else if (live) {
-      t0 = theta[2 * c];
-      t1 = theta[2 * c + 1];
+      a0 = theta[2 * c];
+      a1 = theta[2 * c + 1];
     }
+    Chain<real, TARGET, ALG, NC> ch;
+    ch.init(P, a0, a1);
 
-    // state of the MH chain: value of the target and the proposal centre at theta
-    Eval<real> cur;
-    real cc0 = 0, cc1 = 0, clog = 0;
-    if (ADJ) {
-      eval_target<real, TARGET, NC, false>(P, t0, t1, cur);
-      drift_centre<real, ALG>(P, t0, t1, cur, cc0, cc1);
-      clog = mh_logdens2<real, ALG>(P, t0, t1, cur);
-    }
-
-    double m_n = 0, m_s0 = 0, m_s1 = 0, m_s00 = 0, m_s01 = 0, m_s11 = 0;
-    real b_n = 0, b_s0 = 0, b_s1 = 0, b_s00 = 0, b_s01 = 0, b_s11 = 0;  // 32-step blocks
-    uint32_t nacc = 0;
-    uint4 rnd = make_uint4(0, 0, 0, 0);
-
-    for (long long k = 0; k < K; ++k) {
-      // ---- noise: validation mode reads the host-supplied draws, production mode uses
-      // Philox: one block per step for adjusted samplers (2 normals + 1 uniform), one
-      // block per TWO steps otherwise.
-      real x0, x1, u = 0;
-      if (noise != nullptr) {
-        x0 = live ? noise[(c * K + k) * 2] : real(0);
-        x1 = live ? noise[(c * K + k) * 2 + 1] : real(0);
-        if (ADJ) u = live ? unif[c * K + k] : real(0);
-      } else if (ADJ) {
-        rnd = lmc_philox4x32_10(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), io.key);
-        M::normals(rnd.x, rnd.y, x0, x1);
-        u = M::uniform(rnd.z);
-      } else {
-        if ((k & 1) == 0) {
+    if (PROD) {
+      const long long kb = io.burnin < K ? (io.burnin > 0 ? io.burnin : 0) : K;
+      const bool hist = io.hist != nullptr && io.hist_every > 0;
+      run_production<real, TARGET, ALG, NC, false, false>(ch, P, io, c_lo, c_hi, live, 0, kb);
+      if (hist) run_production<real, TARGET, ALG, NC, true, true>(ch, P, io, c_lo, c_hi, live, kb, K);
+      else run_production<real, TARGET, ALG, NC, true, false>(ch, P, io, c_lo, c_hi, live, kb, K);
+    } else {
+      // validation mode: the reference's own draws come from HBM, every state goes back
+      const real* noise = (const real*)io.noise;
+      const real* unif = (const real*)io.unif;
+      real* traj = (real*)io.traj;
+      uint4 rnd = make_uint4(0, 0, 0, 0);
+      for (long long k = 0; k < K; ++k) {
+        real x0, x1, u = 0;
+        if (noise != nullptr) {
+          x0 = live ? noise[(c * K + k) * 2] : real(0);
+          x1 = live ? noise[(c * K + k) * 2 + 1] : real(0);
+          if (ADJ) u = live ? unif[c * K + k] : real(0);
+        } else if (ADJ) {
+          rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), io.rk);
+          M::normals(rnd.x, rnd.y, x0, x1);
+          u = M::uniform(rnd.z);
+        } else if ((k & 1) == 0) {
           long long kb = k >> 1;
-          rnd = lmc_philox4x32_10(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), io.key);
+          rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), io.rk);
           M::normals(rnd.x, rnd.y, x0, x1);
         } else {
           M::normals(rnd.z, rnd.w, x0, x1);
         }
-      }
-
-      bool emitted = true;
-      if (!ADJ) {
-        step_unadjusted<real, TARGET, ALG, NC>(P, t0, t1, x0, x1);
-      } else {
-        // lmc.py:124-130: propose, MH ratio p(new) q(old|new) / (p(old) q(new|old)),
-        // accept iff u <= min(1, ratio); a NaN ratio accepts (Python's min(1, nan) == 1).
-        real n0 = M::fma(P.s2g, x0, cc0), n1 = M::fma(P.s2g, x1, cc1);
-        Eval<real> prop;
-        eval_target<real, TARGET, NC, false>(P, n0, n1, prop);
-        real pc0, pc1;
-        drift_centre<real, ALG>(P, n0, n1, prop, pc0, pc1);
-        real plog = mh_logdens2<real, ALG>(P, n0, n1, prop);
-        real f0 = t0 - pc0, f1 = t1 - pc1;   // old | new
-        real r0 = n0 - cc0, r1 = n1 - cc1;   // new | old
-        real lq = (M::fma(r0, r0, r1 * r1) - M::fma(f0, f0, f1 * f1)) * P.inv4g;  // natural log
-        real lr2 = (plog - clog) + real(1.4426950408889634) * lq;
-        real ratio = M::exp2(lr2);
-        emitted = !(u > M::min(real(1), ratio));
-        if (emitted) {
-          t0 = n0; t1 = n1; cc0 = pc0; cc1 = pc1; clog = plog;
-          ++nacc;
+        const bool emitted = ch.step(P, x0, x1, u);
+        if (ADJ && io.accept != nullptr && live) io.accept[c * K + k] = emitted ? 1 : 0;
+        if (traj != nullptr && live) {
+          traj[(c * K + k) * 2] = ch.t0;
+          traj[(c * K + k) * 2 + 1] = ch.t1;
         }
-        if (io.accept != nullptr && live) io.accept[c * K + k] = emitted ? 1 : 0;
-      }
-
-      if (traj != nullptr && live) {
-        traj[(c * K + k) * 2] = t0;
-        traj[(c * K + k) * 2 + 1] = t1;
-      }
-      // ---- running statistics over the emitted samples
-      if (k >= io.burnin) {
-        real f = emitted ? real(1) : real(0);
-        b_n += f;
-        b_s0 = M::fma(f, t0, b_s0);
-        b_s1 = M::fma(f, t1, b_s1);
-        b_s00 = M::fma(f * t0, t0, b_s00);
-        b_s01 = M::fma(f * t0, t1, b_s01);
-        b_s11 = M::fma(f * t1, t1, b_s11);
-        if ((k & 31) == 31) {
-          m_n += b_n; m_s0 += b_s0; m_s1 += b_s1; m_s00 += b_s00; m_s01 += b_s01; m_s11 += b_s11;
-          b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = 0;
-        }
-        if (io.hist != nullptr && io.hist_every > 0 && emitted && live && ((k + 1) % io.hist_every == 0)) {
-          int ix = (int)floor(((double)t0 - io.hist_lo) * io.hist_scale);
-          int iy = (int)floor(((double)t1 - io.hist_lo) * io.hist_scale);
-          if (ix >= 0 && ix < io.hist_bins && iy >= 0 && iy < io.hist_bins)
-            atomicAdd(&io.hist[ix * io.hist_bins + iy], 1ull);
+        if (k >= io.burnin) {
+          ch.accumulate(emitted);
+          if ((k & 31) == 31) ch.flush();
+          if (io.hist != nullptr && io.hist_every > 0 && emitted && live && ((k + 1) % io.hist_every == 0))
+            hist_add(io, (double)ch.t0, (double)ch.t1);
         }
       }
+      ch.flush();
     }
-    m_n += b_n; m_s0 += b_s0; m_s1 += b_s1; m_s00 += b_s00; m_s01 += b_s01; m_s11 += b_s11;
 
+    // unadjusted samplers emit every step: the count is known without a per-step add
+    if (!ADJ) ch.m_n = (double)(K - (io.burnin < K ? (io.burnin > 0 ? io.burnin : 0) : K));
+    double m_n = ch.m_n, m_s0 = ch.m_s0, m_s1 = ch.m_s1, m_s00 = ch.m_s00, m_s01 = ch.m_s01, m_s11 = ch.m_s11;
     if (live) {
-      theta[2 * c] = t0;
-      theta[2 * c + 1] = t1;
-      if (io.naccept != nullptr) io.naccept[c] = ADJ ? nacc : (uint32_t)K;
-      if (io.hist != nullptr && io.hist_every == 0) {
-        int ix = (int)floor(((double)t0 - io.hist_lo) * io.hist_scale);
-        int iy = (int)floor(((double)t1 - io.hist_lo) * io.hist_scale);
-        if (ix >= 0 && ix < io.hist_bins && iy >= 0 && iy < io.hist_bins)
-          atomicAdd(&io.hist[ix * io.hist_bins + iy], 1ull);
-      }
+      theta[2 * c] = ch.t0;
+      theta[2 * c + 1] = ch.t1;
+      if (io.naccept != nullptr) io.naccept[c] = ADJ ? ch.nacc : (uint32_t)K;
+      if (io.hist != nullptr && io.hist_every == 0) hist_add(io, (double)ch.t0, (double)ch.t1);
     } else {
       m_n = m_s0 = m_s1 = m_s00 = m_s01 = m_s11 = 0;
     }
@@ -479,24 +601,26 @@ template <typename real>
 __global__ void philox_draws_kernel(int adjusted, long long C, long long K, uint2 key,
                                     unsigned long long chain_offset, real* normals, real* unif, real* theta0) {
   using M = Math<real>;
+  uint32_t rk[20];
+  lmc_philox_round_keys(key, rk);
   long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   unsigned long long gc = chain_offset + (unsigned long long)c;
   uint32_t c_lo = (uint32_t)gc, c_hi = (uint32_t)(gc >> 32);
   if (theta0 != nullptr) {
-    uint4 r = lmc_philox4x32_10(make_uint4(0u, LMC_STREAM_INIT, c_lo, c_hi), key);
+    uint4 r = lmc_philox4x32_10_rk(make_uint4(0u, LMC_STREAM_INIT, c_lo, c_hi), rk);
     M::normals(r.x, r.y, theta0[2 * c], theta0[2 * c + 1]);
   }
   uint4 rnd = make_uint4(0, 0, 0, 0);
   for (long long k = 0; k < K; ++k) {
     real x0, x1;
     if (adjusted) {
-      rnd = lmc_philox4x32_10(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), key);
+      rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), rk);
       M::normals(rnd.x, rnd.y, x0, x1);
       if (unif != nullptr) unif[c * K + k] = M::uniform(rnd.z);
     } else if ((k & 1) == 0) {
       long long kb = k >> 1;
-      rnd = lmc_philox4x32_10(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), key);
+      rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), rk);
       M::normals(rnd.x, rnd.y, x0, x1);
     } else {
       M::normals(rnd.z, rnd.w, x0, x1);
@@ -520,11 +644,13 @@ void fill_params(const lmc_mix_target& T, const lmc_mix_step& S, MixP<real>& P) 
     P.p10[i] = (real)T.prec[i][2]; P.p11[i] = (real)T.prec[i][3];
     P.al[i] = (real)T.alpha[i];
     P.thr[i] = (real)(T.lamda * T.alpha[i]);
+    P.c1[i] = (real)(-1.4426950408889634 * T.alpha[i]);
     double cst = (T.kind == LMC_TARGET_LAPLACE) ? T.omega[i] * (T.alpha[i] / 2) * (T.alpha[i] / 2)
                                                 : T.omega[i] / T.norm[i];
     P.lc[i] = (real)log2(cst);
   }
   P.lamda = (real)T.lamda;
+  P.c2 = (real)(T.lamda != 0 ? -1.4426950408889634 / (2 * T.lamda) : 0.0);
   P.inv_lamda = (real)(T.lamda != 0 ? 1.0 / T.lamda : 0.0);
   P.pr_alpha = (real)T.prior_alpha;
   P.pr_thr = (real)(T.lamda * T.prior_alpha);
@@ -542,12 +668,14 @@ void fill_params(const lmc_mix_target& T, const lmc_mix_step& S, MixP<real>& P) 
   P.pp_thr = (real)(S.eta != 0 ? T.lamda / S.eta : 0.0);
   P.b0 = (real)S.beta[0]; P.b1 = (real)S.beta[1];
   P.sg0 = (real)S.sigma[0]; P.sg1 = (real)S.sigma[1];
+  P.ib0 = (real)(S.beta[0] != 0 ? 1.0 / S.beta[0] : 0.0); P.ib1 = (real)(S.beta[1] != 0 ? 1.0 / S.beta[1] : 0.0);
+  P.isg0 = (real)(S.sigma[0] != 0 ? 1.0 / S.sigma[0] : 0.0); P.isg1 = (real)(S.sigma[1] != 0 ? 1.0 / S.sigma[1] : 0.0);
   P.hshift = (real)S.hess_shift;
 }
 
-template <typename real, int TARGET, int ALG, int NC>
+template <typename real, int TARGET, int ALG, int NC, bool PROD>
 int launch_one(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
-  auto kern = mix_chain_kernel<real, TARGET, ALG, NC>;
+  auto kern = mix_chain_kernel<real, TARGET, ALG, NC, PROD>;
   int dev = 0, sms = 0, occ = 0;
   LMC_CUDA_OK(cudaGetDevice(&dev));
   LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -564,8 +692,11 @@ int launch_one(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
 
 template <typename real, int TARGET, int ALG>
 int launch_nc(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
-  if (P.n == 5) return launch_one<real, TARGET, ALG, 5>(P, io, st);
-  return launch_one<real, TARGET, ALG, 0>(P, io, st);
+  // production = nothing but registers inside the K-loop (Philox noise, no per-step outputs)
+  const bool prod = io.noise == nullptr && io.traj == nullptr && io.accept == nullptr;
+  if (P.n == 5) return prod ? launch_one<real, TARGET, ALG, 5, true>(P, io, st)
+                            : launch_one<real, TARGET, ALG, 5, false>(P, io, st);
+  return prod ? launch_one<real, TARGET, ALG, 0, true>(P, io, st) : launch_one<real, TARGET, ALG, 0, false>(P, io, st);
 }
 
 template <typename real>
@@ -647,6 +778,7 @@ extern "C" int lmc_mix_run(const lmc_mix_target* target, const lmc_mix_step* ste
   io.hist_every = uio->hist_every;
   io.chain_offset = chain_offset;
   io.key = make_key(seed);
+  lmc_philox_round_keys(io.key, io.rk);
   io.init_from_rng = uio->init_from_rng;
   io.hist_bins = uio->hist_bins;
   io.hist_lo = uio->hist_lo;
