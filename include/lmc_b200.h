@@ -190,6 +190,17 @@ int lmc_img_myula_run(const lmc_img_problem* pb, const lmc_img_myula_params* pr,
 int lmc_img_ulpda_run(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, int dtype, int64_t C,
                       int64_t N, uint64_t seed, uint64_t chain_offset, const lmc_img_io* io, void* stream);
 
+/* MYULA with the whole chain state ON CHIP (csrc/img_myula_onchip.cu): one thread-block
+ * cluster of 8 CTAs per chain, x and the TV dual field in (distributed) shared memory for
+ * all N iterations.  Same arguments, noise stream and results (to fp32 rounding) as
+ * lmc_img_myula_run; requires LMC_F32, ny <= 256, nx <= 256, blur taps <= 7 per axis
+ * (lmc_img_myula_onchip_supported() != 0); needs no workspace but io->d_counters.
+ * lmc_img_myula_onchip_clusters(): co-resident clusters on the current device (<0 on error). */
+int lmc_img_myula_onchip_supported(const lmc_img_problem* pb, int dtype);
+int lmc_img_myula_onchip_clusters(void);
+int lmc_img_myula_run_onchip(const lmc_img_problem* pb, const lmc_img_myula_params* pr, int dtype, int64_t C,
+                             int64_t N, uint64_t seed, uint64_t chain_offset, const lmc_img_io* io, void* stream);
+
 /* Unit entry points (operators of SURVEY 8a rows I1-I5), batched over C images.
  * d_in/d_out are (C,P) unless stated; workspace as for the sampler of the same family. */
 int lmc_img_blur(const lmc_img_problem* pb, int dtype, int adjoint, int64_t C, const void* d_in, void* d_out,

@@ -260,24 +260,42 @@ class DeconvEngine:
         return {"tv_sweeps": int(c[0]), "lsqr_iterations": int(c[1]), "lsqr_solves": int(c[2])}
 
     # ------------------------------------------------------------------ MYULA
+    def onchip_supported(self):
+        """True when the on-chip cluster kernel (csrc/img_myula_onchip.cu) covers this problem."""
+        pb = self._problem()
+        return bool(self.lib.lmc_img_myula_onchip_supported(C.byref(pb), _dt(self.dtype)))
+
     def myula(self, x, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, epsg=1.0, seed=0, chain_offset=0,
-              noise=None, samples=None, mean=None, m2=None, burnin=0, stat_count0=0, iter_offset=0):
-        """Advances the (C,P) device tensor ``x`` in place by N MYULA iterations (algs.py:564-583)."""
+              noise=None, samples=None, mean=None, m2=None, burnin=0, stat_count0=0, iter_offset=0,
+              engine="auto"):
+        """Advances the (C,P) device tensor ``x`` in place by N MYULA iterations (algs.py:564-583).
+
+        ``engine``: "onchip" = cluster kernel with the chain state in shared memory (fp32, images up to
+        256 x 256), "stream" = tiled kernel through HBM (any size, fp32/fp64), "auto" = on-chip when
+        it applies.  Both are CUDA; there is no CPU path."""
         torch, lib = self.torch, self.lib
         Cn = x.shape[0]
         pr = _lib.ImgMyulaParams()
         pr.tau, pr.gamma, pr.epsg = float(tau), float(gamma), float(epsg)
         pr.tv_sigma, pr.tv_rtol, pr.tv_niter = float(tv_sigma), float(tv_rtol), int(tv_niter)
-        nb = lib.lmc_img_myula_workspace_bytes(_dt(self.dtype), self.dims[0], self.dims[1], Cn)
-        ws = torch.empty(nb, dtype=torch.uint8, device=self.dev)
+        if engine not in ("auto", "onchip", "stream"):
+            raise ValueError("engine must be 'auto', 'onchip' or 'stream'")
+        onchip = engine == "onchip" or (engine == "auto" and self.onchip_supported())
+        if onchip:
+            ws = torch.empty(256, dtype=torch.uint8, device=self.dev)
+        else:
+            nb = lib.lmc_img_myula_workspace_bytes(_dt(self.dtype), self.dims[0], self.dims[1], Cn)
+            ws = torch.empty(nb, dtype=torch.uint8, device=self.dev)
         nz = self._noise(noise, Cn, N)
         io = self._io(Cn, N, nz, samples, mean, m2, burnin, stat_count0, iter_offset, ws)
         io.d_x = x.data_ptr()
         pb = self._problem()
+        fn, name = ((lib.lmc_img_myula_run_onchip, "lmc_img_myula_run_onchip") if onchip
+                    else (lib.lmc_img_myula_run, "lmc_img_myula_run"))
         with torch.cuda.device(self.dev):
-            rc = lib.lmc_img_myula_run(C.byref(pb), C.byref(pr), _dt(self.dtype), Cn, int(N), seed & (2 ** 64 - 1),
-                                       int(chain_offset), C.byref(io), _stream(torch, self.dev))
-        _lib.check(rc, "lmc_img_myula_run")
+            rc = fn(C.byref(pb), C.byref(pr), _dt(self.dtype), Cn, int(N), seed & (2 ** 64 - 1),
+                    int(chain_offset), C.byref(io), _stream(torch, self.dev))
+        _lib.check(rc, name)
         return ws, nz   # keep alive until the caller synchronises
 
     # ------------------------------------------------------------------ ULPDA
@@ -331,13 +349,13 @@ class DeconvEngine:
 
     # ------------------------------------------------------------------ many-chain production runs
     def run_myula(self, chains, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, seed=0, chain_offset=0,
-                  burnin=0, x0=None, second_moment=True, sync=True) -> ImageStats:
+                  burnin=0, x0=None, second_moment=True, sync=True, engine="auto") -> ImageStats:
         torch = self.torch
         x = self._buf(x0, chains)
         mean = torch.zeros((chains, self.P), dtype=self.tdt, device=self.dev)
         m2 = torch.zeros_like(mean) if second_moment else None
         keep = self.myula(x, N, tau, gamma, tv_sigma, tv_niter, tv_rtol, seed=seed, chain_offset=chain_offset,
-                          mean=mean, m2=m2, burnin=burnin)
+                          mean=mean, m2=m2, burnin=burnin, engine=engine)
         if sync:
             torch.cuda.current_stream(self.dev).synchronize()
             keep = None

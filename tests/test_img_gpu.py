@@ -203,7 +203,8 @@ def test_ulpda_trajectory_fp64(torch, dims, kernel, iso, gfirst):
     assert c["lsqr_iterations"] == sum(l2.lsqr_itn), (c, l2.lsqr_itn)
 
 
-def test_myula_fp32_within_tolerance(torch):
+@pytest.mark.parametrize("engine", ["stream", "onchip"])
+def test_myula_fp32_within_tolerance(torch, engine):
     from lmc_atomi_b200 import imaging as I
     from oracle import deconv_ref as D
     dims, N = (64, 64), 25
@@ -215,10 +216,11 @@ def test_myula_fp32_within_tolerance(torch):
     eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float32")
     x = torch.zeros((1, P), dtype=torch.float32, device="cuda")
     samples = torch.empty((1, N, P), dtype=torch.float32, device="cuda")
-    eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise[None], samples=samples)
+    eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise[None], samples=samples,
+              engine=engine)
     got = samples.cpu().numpy()[0]
     err = max(rel(got[n], want[n]) for n in range(N))
-    print(f"MYULA fp32 free-run rel err over {N} iterations: {err:.3e}")
+    print(f"MYULA fp32 ({engine}) free-run rel err over {N} iterations: {err:.3e}")
     assert err < 1e-5
 
 
