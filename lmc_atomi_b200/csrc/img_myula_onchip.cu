@@ -7,20 +7,25 @@
 // columns each side = the zero boundary of pylops Convolve2D):
 //   XS   : x on the CTA's rows plus 6 halo rows above and below (blur halo)
 //   pool : two (rr, ss) buffers of the TV dual field, RPC + 2 halo rows each; the
-//          second pair doubles as the two scratch images of the blur passes
+//          second pair doubles as the scratch image of the blur passes
+//   BS   : `base` = everything of the MYULA update that does not depend on the TV prox
 // and in registers (thread = one column x a strip of RPC/2 rows): the pointwise
-// arrays p, q (current projected dual iterate) and `base` (everything of the MYULA
-// update that does not depend on the TV prox).  Halo rows are PUSHED into the
+// arrays p, q (current projected dual iterate).  Halo rows are PUSHED into the
 // neighbour CTA's shared memory (DSMEM) by the thread that produces them; the
 // per-chain TV objective is reduced across the cluster through 8 doubles per CTA.
 // One cluster barrier per TV sweep + one per sampler iteration; chains exit the
 // TV loop individually (no batch-wide lockstep).  HBM traffic per iteration: the
 // observation b (L2 resident when shared), the running mean / samples if requested.
 //
+// The blur H^T(Hx - b) is two fused separable passes with compile-time tap counts
+// (5, 6, 7 = the reference's H5/H6/H7): a horizontal 1-D filter out of shared memory
+// feeding a vertical sliding window held in registers.
+//
 // Arithmetic is the same recipe as the streaming kernel img_myula.cu (pyproximal
-// TV.prox as restated in SURVEY 8a I4) with two fp32 shortcuts that stay far inside
+// TV.prox as restated in SURVEY 8a I4) with fp32 shortcuts that stay far inside
 // the 1e-5 trajectory tolerance: dx/(8 gamma) is a multiply by the host-rounded
-// reciprocal, and r / max(1,|(r,s)|) is r * min(1, rsqrt(r^2+s^2)).
+// reciprocal, r / max(1,|(r,s)|) is r * min(1, rsqrt(r^2+s^2)), and the objective
+// is summed in fp32 over groups of 4 pixels before it enters the fp64 accumulator.
 #include <cooperative_groups.h>
 
 #include "img_common.cuh"
@@ -43,15 +48,17 @@ struct OcLayout {
   static constexpr int STRIP = RPC / 2;
   static constexpr int XS_ROWS = RPC + 2 * OC_HB;
   static constexpr int DROWS = RPC + 2;             // halo row above, own rows, halo row below
-  static constexpr int T_ROWS = RPC + 2 * OC_HB;    // blur scratch images
+  static constexpr int T_ROWS = RPC + 2 * OC_HB;    // blur scratch image (residual), local row a at T2 + a + OC_HB
   // pool rows.  Buffer Y (odd TV sweeps write it) aliases the blur scratch; buffer X
   // (written by sweep 0, which runs before the blur of the same iteration) does not.
   static constexpr int Y_RR = 0, Y_SS = DROWS;
-  static constexpr int T1 = 0, T2 = T_ROWS;
-  static constexpr int X_RR = (2 * DROWS > 2 * T_ROWS) ? 2 * DROWS : 2 * T_ROWS;
+  static constexpr int T2 = 0;
+  static constexpr int X_RR = (2 * DROWS > T_ROWS) ? 2 * DROWS : T_ROWS;
   static constexpr int X_SS = X_RR + DROWS;
   static constexpr int POOL_ROWS = X_SS + DROWS;
-  static constexpr size_t SMEM_BYTES = (size_t)(XS_ROWS + POOL_ROWS) * OC_PITCH * sizeof(float);
+  static constexpr int PADDED_FLOATS = (XS_ROWS + POOL_ROWS) * OC_PITCH;
+  static constexpr int BS_FLOATS = RPC * OC_W;      // pointwise: no pad columns
+  static constexpr size_t SMEM_BYTES = (size_t)(PADDED_FLOATS + BS_FLOATS) * sizeof(float);
   static_assert(STRIP % 4 == 0, "strips are processed in groups of 4 rows (one Philox block per lane)");
   static_assert(RPC >= OC_HB, "halo rows must come from the adjacent CTA only");
 };
@@ -74,11 +81,10 @@ struct OcArgs {
   double tv_rtol;
 };
 
+// c_it = (t_{it-1} - 1) / t_it with t_k = t_{k-1} + 1/2, t_0 = 1 (fista_c() of img_myula.cu,
+// the "sic" recurrence of SURVEY I4) in closed form: (it - 1) / (it + 2).
 __device__ __forceinline__ float oc_fista_c(int it) {
-  // same recurrence as fista_c() of img_myula.cu: t_k = t_{k-1} + 1/2 (sic)
-  if (it < 1) return 0.0f;
-  double told = 1.0 + 0.5 * (it - 1), t = (1.0 + sqrt(4.0 * told * told)) / 2.0;
-  return (float)((told - 1.0) / t);
+  return it < 1 ? 0.0f : (float)(it - 1) / (float)(it + 2);
 }
 
 // sol = x - gamma * div(rr, ss), div = -grad^T, accumulated in the order of sol_at() (img_myula.cu)
@@ -106,9 +112,9 @@ __device__ __forceinline__ void oc_transpose4(float v[4], int m) {
 // Per-thread view of the CTA's shared memory and of the neighbours' windows.
 template <int RPC>
 struct OcCtx {
-  using L = OcLayout<RPC>;
   float* xs;
   float* pool;
+  float* bs;
   float* xs_prev;
   float* xs_next;
   float* pool_prev;
@@ -116,22 +122,24 @@ struct OcCtx {
   int rank, c, h, r0, a0, ny, nx;
   bool colin, has_right;
   __device__ __forceinline__ float& XS(int a, int cc) const { return xs[(a + OC_HB) * OC_PITCH + OC_PADL + cc]; }
-  // pool row `row` (buffers store local row a at row base + a + 1; scratch images at base + a + OC_HB)
+  // pool row `row` (dual buffers store local row a at row base + a + 1; the scratch image at base + a + OC_HB)
   __device__ __forceinline__ float& PL(int row, int cc) const { return pool[row * OC_PITCH + OC_PADL + cc]; }
+  __device__ __forceinline__ float& BS(int a) const { return bs[a * OC_W + c]; }
 };
 
 // One TV dual sweep on the thread's strip.  Reads (rr_it, ss_it) from buffer `cur`, leaves
 // p_{it+1} in (P, Q) and writes rr_{it+1} = p_{it+1} + cn (p_{it+1} - p_it) into buffer `nxt`
 // (own rows, plus the halo rows of the neighbour CTAs).  Returns the thread's part of the
 // objective 1/2 ||x - sol||^2 + gamma sum |grad sol|.  FIRST: rr_0 = ss_0 = 0, sol_0 = x.
-template <int RPC, bool FIRST>
+// FULL: the image fills the cluster's 8*RPC x 256 footprint (no in-image masks).
+template <int RPC, bool FIRST, bool FULL>
 __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, int cur_ss, int nxt_rr, int nxt_ss,
                                               float cn, float gamma, float inv_g8,
                                               float (&P)[RPC / 2], float (&Q)[RPC / 2]) {
   constexpr int STRIP = RPC / 2;
   const int c = K.c, a0 = K.a0;
   double acc = 0.0;
-  float accf = 0.0f;
+  float accn = 0.0f, accd = 0.0f;
   float x_c = K.XS(a0, c), rr_c = 0.0f, ss_c = 0.0f, rr_ur = 0.0f, sol_c;
   if (FIRST) {
     sol_c = x_c;
@@ -141,6 +149,7 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
     sol_c = oc_sol(x_c, rr_c, K.PL(cur_rr + a0, c), ss_c, K.PL(cur_ss + a0 + 1, c - 1), gamma);
     rr_ur = K.PL(cur_rr + a0, c + 1);
   }
+  const bool last_cta = K.rank == OC_CL - 1;
 #pragma unroll
   for (int k = 0; k < STRIP; ++k) {
     const int a = a0 + k, i = K.r0 + a;
@@ -157,20 +166,28 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
       sol_r = oc_sol(x_r, rr_r, rr_ur, K.PL(cur_ss + a + 1, c + 1), ss_c, gamma);
       rr_ur = rr_r;
     }
-    const bool in = K.colin && i < K.ny;
-    const float dx = (i < K.ny - 1) ? sol_b - sol_c : 0.0f;
+    bool in, has_below;
+    if (FULL) {
+      in = true;
+      has_below = !(k == STRIP - 1 && K.h == 1 && last_cta);
+    } else {
+      in = K.colin && i < K.ny;
+      has_below = i < K.ny - 1;
+    }
+    const float dx = has_below ? sol_b - sol_c : 0.0f;
     const float dy = K.has_right ? sol_r - sol_c : 0.0f;
     const float nrm = lmc_sqrtf(fmaf(dx, dx, dy * dy));
     if (in) {
       if (!FIRST) {
-        const double df = (double)(x_c - sol_c);
-        acc = fma(0.5 * df, df, acc);
+        const float df = x_c - sol_c;
+        accd = fmaf(df, df, accd);
       }
-      accf += nrm;
+      accn += nrm;
     }
-    if ((k & 3) == 3) {          // |grad sol| summed in fp32 over 4 pixels, then in fp64
-      acc = fma((double)gamma, (double)accf, acc);
-      accf = 0.0f;
+    if ((k & 3) == 3) {          // fp32 over 4 pixels, then fp64
+      acc = fma((double)gamma, (double)accn, acc);
+      if (!FIRST) acc = fma(0.5, (double)accd, acc);
+      accn = accd = 0.0f;
     }
     // projected dual update: r = rr - dx/(8 gamma); p = r / max(1, |(r,s)|)
     const float r = fmaf(-dx, inv_g8, rr_c), s = fmaf(-dy, inv_g8, ss_c);
@@ -199,7 +216,7 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
       }
     }
     if (k == STRIP - 1 && K.h == 1) {  // last own row -> above-halo of the next CTA
-      if (K.rank < OC_CL - 1) {
+      if (!last_cta) {
         K.pool_next[(nxt_rr + 0) * OC_PITCH + OC_PADL + c] = rrn;
       } else {
         K.PL(nxt_rr + RPC + 1, c) = 0.0f;
@@ -214,70 +231,93 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
   return acc;
 }
 
-// g = H^T mask(H x - b) by four separable passes through the scratch images, fused with the
-// noise draw:  base = (1 - tau/gamma) x - tau sigma_L2 g + sqrt(2 tau) xi      (algs.py:569)
-template <int RPC>
+// g = H^T mask(H x - b) in two fused separable passes (NT taps per axis, compile time), each a
+// horizontal filter out of shared memory feeding a vertical sliding window in registers:
+//   AB: x -> residual  (scratch image T2, rows [-hi_y, RPC - lo_y) of the CTA)
+//   CD: residual -> g on the thread's own strip, fused with the noise draw:
+//       base = (1 - tau/gamma) x - tau sigma_L2 g + sqrt(2 tau) xi      (algs.py:569)  -> BS
+template <int RPC, int NT, bool FULL>
 __device__ __forceinline__ void oc_blur_base(const OcCtx<RPC>& K, const OcArgs& A, long long chain, long long n,
-                                             unsigned long long it_global, float (&base)[RPC / 2]) {
+                                             unsigned long long it_global) {
   using L = OcLayout<RPC>;
   constexpr int STRIP = RPC / 2;
+  constexpr int TOT = RPC + NT - 1, HALF = (TOT + 1) / 2;
   const Geom<float>& g = A.g;
-  const int c = K.c, h = K.h, a0 = K.a0, r0 = K.r0, ny = K.ny, nx = K.nx;
-  const int ey = g.ntap_y - 1, hi_y = g.lo_y + g.ntap_y - 1;
-  // A: forward row pass  XS -> T1 on rows [-ey, RPC+ey)
-  for (int a = -ey + h; a < RPC + ey; a += 2) {
-    float s = 0.0f;
-    for (int t = 0; t < g.ntap_x; ++t) s = fmaf(g.wx[t], K.XS(a, c + g.lo_x + t), s);
-    K.PL(L::T1 + a + OC_HB, c) = s;
+  const int c = K.c, a0 = K.a0, r0 = K.r0, ny = K.ny, nx = K.nx;
+  const int lo_y = g.lo_y, lo_x = g.lo_x, hi_y = lo_y + NT - 1;
+  float wx[NT], wy[NT];
+#pragma unroll
+  for (int t = 0; t < NT; ++t) {
+    wx[t] = g.wx[t];
+    wy[t] = g.wy[t];
   }
-  __syncthreads();
-  // B: forward column pass - b, masked to the image  T1 -> T2 on rows [-hi_y, RPC-lo_y)
+  // ---- AB
   {
+    const int j0 = K.h * HALF;
+    const int aout0 = -hi_y + j0;          // first residual row of this thread
+    const int rin0 = aout0 + lo_y;         // first x row it reads
     const float* bc = A.b + chain * A.b_stride;
-    for (int a = -hi_y + h; a < RPC - g.lo_y; a += 2) {
-      const int i = r0 + a;
-      float s = 0.0f;
-      if (K.colin && i >= 0 && i < ny) {
-        const float bv = __ldg(bc + (long long)i * nx + c);
-        for (int t = 0; t < g.ntap_y; ++t) s = fmaf(g.wy[t], K.PL(L::T1 + a + g.lo_y + t + OC_HB, c), s);
-        s -= bv;
+    const float* xrow = &K.XS(rin0, c + lo_x);
+    float win[NT];
+#pragma unroll
+    for (int jj = 0; jj < HALF + NT - 1; ++jj) {
+      float t1 = 0.0f;
+      if (rin0 + jj < RPC + OC_HB) {
+#pragma unroll
+        for (int s = 0; s < NT; ++s) t1 = fmaf(wx[s], xrow[jj * OC_PITCH + s], t1);
       }
-      K.PL(L::T2 + a + OC_HB, c) = s;
+      win[jj % NT] = t1;
+      if (jj >= NT - 1) {
+        const int o = jj - (NT - 1), a = aout0 + o, i = r0 + a;
+        if (j0 + o < TOT) {
+          float res = 0.0f;
+          const bool in = FULL ? (i >= 0 && i < ny) : (K.colin && i >= 0 && i < ny);
+          if (in) {
+            const float bv = __ldg(bc + (long long)i * nx + c);
+#pragma unroll
+            for (int t = 0; t < NT; ++t) res = fmaf(wy[t], win[(o + t) % NT], res);
+            res -= bv;
+          }
+          K.PL(L::T2 + a + OC_HB, c) = res;
+        }
+      }
     }
   }
   __syncthreads();
-  // C: adjoint row pass  T2 -> T1 (same rows)
-  for (int a = -hi_y + h; a < RPC - g.lo_y; a += 2) {
-    float s = 0.0f;
-    for (int t = 0; t < g.ntap_x; ++t) s = fmaf(g.wx[t], K.PL(L::T2 + a + OC_HB, c - g.lo_x - t), s);
-    K.PL(L::T1 + a + OC_HB, c) = s;
-  }
-  __syncthreads();
-  // D: adjoint column pass on the own strip
-  const int quads_per_row = (nx + 3) / 4;
-#pragma unroll
-  for (int k4 = 0; k4 < STRIP; k4 += 4) {
+  // ---- CD
+  {
+    const int rin0 = a0 - hi_y;
+    const float* rrow = &K.PL(L::T2 + rin0 + OC_HB, c - lo_x);
+    const int quads_per_row = (nx + 3) / 4;
+    float win[NT];
     float z[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-    if (A.noise == nullptr) {
-      const int m = c & 3;
-      img_noise4<float>(A.key, A.chain_offset + (unsigned long long)chain, it_global, r0 + a0 + k4 + m, c >> 2,
-                        quads_per_row, z);
-      oc_transpose4(z, m);
-    }
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
-      const int k = k4 + kk, a = a0 + k, i = r0 + a;
-      float s = 0.0f;
-      for (int t = 0; t < g.ntap_y; ++t) s = fmaf(g.wy[t], K.PL(L::T1 + a - g.lo_y - t + OC_HB, c), s);
-      float xi = z[kk];
-      if (A.noise != nullptr && K.colin && i < ny)
-        xi = __ldg(A.noise + (chain * A.N + n) * g.P + (long long)i * nx + c);
-      base[k] = A.a_x * K.XS(a, c) - A.tau * (A.sigma_l2 * s) + A.s2t * xi;
+    for (int jj = 0; jj < STRIP + NT - 1; ++jj) {
+      float u = 0.0f;
+#pragma unroll
+      for (int s = 0; s < NT; ++s) u = fmaf(wx[s], rrow[jj * OC_PITCH - s], u);
+      win[jj % NT] = u;
+      if (jj >= NT - 1) {
+        const int k = jj - (NT - 1), a = a0 + k, i = r0 + a;
+        if ((k & 3) == 0 && A.noise == nullptr) {
+          const int m = c & 3;
+          img_noise4<float>(A.key, A.chain_offset + (unsigned long long)chain, it_global, i + m, c >> 2,
+                            quads_per_row, z);
+          oc_transpose4(z, m);
+        }
+        float gv = 0.0f;
+#pragma unroll
+        for (int t = 0; t < NT; ++t) gv = fmaf(wy[t], win[(k + NT - 1 - t) % NT], gv);
+        float xi = z[k & 3];
+        if (A.noise != nullptr && K.colin && i < ny)
+          xi = __ldg(A.noise + (chain * A.N + n) * g.P + (long long)i * nx + c);
+        K.BS(a) = A.a_x * K.XS(a, c) - A.tau * (A.sigma_l2 * gv) + A.s2t * xi;
+      }
     }
   }
 }
 
-template <int RPC>
+template <int RPC, int NT, bool FULL>
 __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid_constant__ OcArgs A) {
   using L = OcLayout<RPC>;
   constexpr int STRIP = L::STRIP;
@@ -292,6 +332,7 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
   OcCtx<RPC> K;
   K.xs = reinterpret_cast<float*>(smem_raw);
   K.pool = K.xs + L::XS_ROWS * OC_PITCH;
+  K.bs = K.xs + L::PADDED_FLOATS;
   K.rank = (int)cluster.block_rank();
   K.c = tid & (OC_W - 1);
   K.h = tid >> 8;
@@ -299,12 +340,12 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
   K.nx = g.nx;
   K.r0 = K.rank * RPC;
   K.a0 = K.h * STRIP;
-  K.colin = K.c < g.nx;
+  K.colin = FULL ? true : K.c < g.nx;
   K.has_right = K.c < g.nx - 1;
   const int rank = K.rank, c = K.c, h = K.h, r0 = K.r0, a0 = K.a0, ny = g.ny, nx = g.nx;
   const float gamma = A.tv_gamma, inv_g8 = A.inv_g8;
 
-  for (int idx = tid; idx < (L::XS_ROWS + L::POOL_ROWS) * OC_PITCH; idx += OC_NT) K.xs[idx] = 0.0f;
+  for (int idx = tid; idx < L::PADDED_FLOATS; idx += OC_NT) K.xs[idx] = 0.0f;
   // neighbour windows (DSMEM)
   K.xs_prev = rank > 0 ? cluster.map_shared_rank(K.xs, rank - 1) : nullptr;
   K.xs_next = rank < OC_CL - 1 ? cluster.map_shared_rank(K.xs, rank + 1) : nullptr;
@@ -328,7 +369,7 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
     __syncthreads();
 
     for (long long n = 0; n < A.N; ++n) {
-      float P[STRIP], Q[STRIP], base[STRIP];
+      float P[STRIP], Q[STRIP];
       double prev_obj = 0.0;
       int kf = 0;
       const unsigned long long it_global = A.iter_offset + (unsigned long long)n;
@@ -340,14 +381,15 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
         const int nxt_rr = (it & 1) ? L::Y_RR : L::X_RR, nxt_ss = (it & 1) ? L::Y_SS : L::X_SS;
         double acc;
         if (it == 0) {
-          acc = oc_tv_sweep<RPC, true>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, 0.0f, gamma, inv_g8, P, Q);
+          acc = oc_tv_sweep<RPC, true, FULL>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, 0.0f, gamma, inv_g8, P, Q);
         } else {
-          acc = oc_tv_sweep<RPC, false>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, oc_fista_c(it + 1), gamma, inv_g8, P, Q);
+          acc = oc_tv_sweep<RPC, false, FULL>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, oc_fista_c(it + 1), gamma, inv_g8,
+                                              P, Q);
         }
         acc = lmc_warp_sum(acc);
         if (lane == 0) red[wid] = acc;
         // the data-term gradient does not depend on the TV loop: it runs between sweep 0 and its barrier
-        if (it == 0) oc_blur_base<RPC>(K, A, chain, n, it_global, base);
+        if (it == 0) oc_blur_base<RPC, NT, FULL>(K, A, chain, n, it_global);
         __syncthreads();    // red[] complete (and, on sweep 0, the scratch reads are done)
         if (tid < OC_CL) {
           double s = 0.0;
@@ -361,18 +403,27 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
 #pragma unroll
         for (int r = 0; r < OC_CL; ++r) obj += cpart[it & 1][r];
         const double prev = it == 0 ? 0.0 : prev_obj;
-        const double rel = obj > 1e-10 ? fabs(obj - prev) / obj : 2.0;
+        // rel = |obj - prev| / obj < rtol  (2 when obj <= 1e-10: never stops)
+        const bool small = obj > 1e-10 && fabs(obj - prev) < A.tv_rtol * obj;
         prev_obj = obj;
         kf = it;
         ++sweeps_done;
-        const bool stop = rel < A.tv_rtol || it == A.tv_niter - 1;
-        if (stop || it + 1 >= A.tv_niter) break;
+        if (small || it + 1 >= A.tv_niter) break;
       }
 
       // ============================================================ update
       // prox = sol_kf = x - gamma div(rr_kf);  x <- base + (tau/gamma) prox; halo rows pushed to the neighbours
       {
+        const bool stats = (A.mean != nullptr) && ((long long)it_global >= A.burnin);
+        const long long o0 = (long long)(r0 + a0) * nx + c;
+        float* const mp = A.mean + chain * g.P + o0;
+        float mv[STRIP];
+        if (stats && K.colin) {
+#pragma unroll
+          for (int k = 0; k < STRIP; ++k) mv[k] = (FULL || r0 + a0 + k < ny) ? mp[(long long)k * nx] : 0.0f;
+        }
         const int cur_rr = (kf & 1) ? L::X_RR : L::Y_RR, cur_ss = (kf & 1) ? L::X_SS : L::Y_SS;
+        float xn[STRIP];
         float rr_up = kf > 0 ? K.PL(cur_rr + a0, c) : 0.0f;
 #pragma unroll
         for (int k = 0; k < STRIP; ++k) {
@@ -384,46 +435,37 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
             sol = oc_sol(xv, rr, rr_up, K.PL(cur_ss + a + 1, c), K.PL(cur_ss + a + 1, c - 1), gamma);
             rr_up = rr;
           }
-          const float xn = fmaf(A.tog, sol, base[k]);
-          base[k] = xn;
-          if (K.colin && i < ny) {
-            K.XS(a, c) = xn;
-            if (a < OC_HB && rank > 0) K.xs_prev[(RPC + a + OC_HB) * OC_PITCH + OC_PADL + c] = xn;
-            if (a >= RPC - OC_HB && rank < OC_CL - 1) K.xs_next[(a - RPC + OC_HB) * OC_PITCH + OC_PADL + c] = xn;
+          xn[k] = fmaf(A.tog, sol, K.BS(a));
+          if (FULL || (K.colin && i < ny)) {
+            K.XS(a, c) = xn[k];
+            if (a < OC_HB && rank > 0) K.xs_prev[(RPC + a + OC_HB) * OC_PITCH + OC_PADL + c] = xn[k];
+            if (a >= RPC - OC_HB && rank < OC_CL - 1) K.xs_next[(a - RPC + OC_HB) * OC_PITCH + OC_PADL + c] = xn[k];
           }
         }
-        const bool stats = (A.mean != nullptr) && ((long long)it_global >= A.burnin);
-        if (K.colin && (A.samples != nullptr || stats)) {
-          const long long o0 = (long long)(r0 + a0) * nx + c;
-          if (A.samples != nullptr) {
-            float* sp = A.samples + (chain * A.N + n) * g.P + o0;
+        if (K.colin && A.samples != nullptr) {
+          float* sp = A.samples + (chain * A.N + n) * g.P + o0;
 #pragma unroll
-            for (int k = 0; k < STRIP; ++k)
-              if (r0 + a0 + k < ny) sp[(long long)k * nx] = base[k];
-          }
-          if (stats) {
-            const float cntn = (float)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
-            float* mp = A.mean + chain * g.P + o0;
-            float mv[STRIP];
+          for (int k = 0; k < STRIP; ++k)
+            if (FULL || r0 + a0 + k < ny) sp[(long long)k * nx] = xn[k];
+        }
+        if (stats && K.colin) {
+          const float inv_cnt = 1.0f / (float)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
+          if (A.m2 != nullptr) {
+            float* m2p = A.m2 + chain * g.P + o0;
+            float m2v[STRIP];
 #pragma unroll
-            for (int k = 0; k < STRIP; ++k) mv[k] = (r0 + a0 + k < ny) ? mp[(long long)k * nx] : 0.0f;
-            if (A.m2 != nullptr) {
-              float* m2p = A.m2 + chain * g.P + o0;
-              float m2v[STRIP];
-#pragma unroll
-              for (int k = 0; k < STRIP; ++k) m2v[k] = (r0 + a0 + k < ny) ? m2p[(long long)k * nx] : 0.0f;
-#pragma unroll
-              for (int k = 0; k < STRIP; ++k) {
-                const float d = base[k] - mv[k];
-                const float mnew = mv[k] + d / cntn;
-                if (r0 + a0 + k < ny) m2p[(long long)k * nx] = m2v[k] + d * (base[k] - mnew);
-              }
-            }
+            for (int k = 0; k < STRIP; ++k) m2v[k] = (FULL || r0 + a0 + k < ny) ? m2p[(long long)k * nx] : 0.0f;
 #pragma unroll
             for (int k = 0; k < STRIP; ++k) {
-              const float d = base[k] - mv[k];
-              if (r0 + a0 + k < ny) mp[(long long)k * nx] = mv[k] + d / cntn;
+              const float d = xn[k] - mv[k];
+              const float mnew = fmaf(d, inv_cnt, mv[k]);
+              if (FULL || r0 + a0 + k < ny) m2p[(long long)k * nx] = fmaf(d, xn[k] - mnew, m2v[k]);
             }
+          }
+#pragma unroll
+          for (int k = 0; k < STRIP; ++k) {
+            const float d = xn[k] - mv[k];
+            if (FULL || r0 + a0 + k < ny) mp[(long long)k * nx] = fmaf(d, inv_cnt, mv[k]);
           }
         }
       }
@@ -445,32 +487,53 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
   cluster.sync();      // no CTA exits while a neighbour may still push into its shared memory
 }
 
-template <int RPC>
-int launch_onchip(const OcArgs& A, cudaStream_t st) {
-  using L = OcLayout<RPC>;
-  auto kern = img_myula_onchip_kernel<RPC>;
-  LMC_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+cudaLaunchConfig_t oc_config(cudaLaunchAttribute* attr, size_t smem, cudaStream_t st) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = OC_CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.blockDim = dim3(OC_NT);
-  cfg.dynamicSmemBytes = L::SMEM_BYTES;
+  cfg.gridDim = dim3(OC_CL);
+  cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cfg.gridDim = dim3(OC_CL);
+  return cfg;
+}
+
+template <int RPC, int NT, bool FULL>
+int oc_max_clusters(int* out) {
+  using L = OcLayout<RPC>;
+  auto kern = img_myula_onchip_kernel<RPC, NT, FULL>;
+  LMC_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+  cudaLaunchAttribute attr[1];
+  cudaLaunchConfig_t cfg = oc_config(attr, L::SMEM_BYTES, nullptr);
+  LMC_CUDA_OK(cudaOccupancyMaxActiveClusters(out, kern, &cfg));
+  return 0;
+}
+
+template <int RPC, int NT, bool FULL>
+int launch_onchip(const OcArgs& A, cudaStream_t st) {
+  using L = OcLayout<RPC>;
+  auto kern = img_myula_onchip_kernel<RPC, NT, FULL>;
   int max_clusters = 0;
-  LMC_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
+  if (oc_max_clusters<RPC, NT, FULL>(&max_clusters) != 0) return -2;
   LMC_REQUIRE(max_clusters >= 1, "on-chip MYULA kernel: no cluster of %d CTAs with %zu B shared memory fits", OC_CL,
               L::SMEM_BYTES);
-  long long ncl = A.C < max_clusters ? A.C : max_clusters;
+  cudaLaunchAttribute attr[1];
+  cudaLaunchConfig_t cfg = oc_config(attr, L::SMEM_BYTES, st);
+  const long long ncl = A.C < max_clusters ? A.C : max_clusters;
   cfg.gridDim = dim3((unsigned)(ncl * OC_CL));
   LMC_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, A));
   return 0;
+}
+
+template <int NT>
+int launch_onchip_nt(const OcArgs& A, cudaStream_t st) {
+  const bool full = A.g.ny == OC_CL * 32 && A.g.nx == OC_W;
+  return full ? launch_onchip<32, NT, true>(A, st) : launch_onchip<32, NT, false>(A, st);
 }
 
 }  // namespace
@@ -478,34 +541,13 @@ int launch_onchip(const OcArgs& A, cudaStream_t st) {
 extern "C" int lmc_img_myula_onchip_supported(const lmc_img_problem* pb, int dtype) {
   if (pb == nullptr || dtype != LMC_F32) return 0;
   if (pb->ny < 1 || pb->nx < 1 || pb->ny > OC_CL * 32 || pb->nx > OC_W) return 0;
-  if (pb->ntap_y < 1 || pb->ntap_x < 1 || pb->ntap_y > OC_HB + 1 || pb->ntap_x > OC_HB + 1) return 0;
+  if (pb->ntap_y != pb->ntap_x || pb->ntap_y < 5 || pb->ntap_y > 7) return 0;   // H5 / H6 / H7
   return 1;
 }
 
 extern "C" int lmc_img_myula_onchip_clusters(void) {
-  auto kern = img_myula_onchip_kernel<32>;
-  using L = OcLayout<32>;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES) != cudaSuccess) {
-    lmc_set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(cudaGetLastError()));
-    return -2;
-  }
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = OC_CL;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.blockDim = dim3(OC_NT);
-  cfg.gridDim = dim3(OC_CL);
-  cfg.dynamicSmemBytes = L::SMEM_BYTES;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) {
-    lmc_set_error("cudaOccupancyMaxActiveClusters failed: %s", cudaGetErrorString(cudaGetLastError()));
-    return -2;
-  }
+  if (oc_max_clusters<32, 5, true>(&n) != 0) return -2;
   return n;
 }
 
@@ -515,8 +557,8 @@ extern "C" int lmc_img_myula_run_onchip(const lmc_img_problem* pb, const lmc_img
   if (check_problem(pb, "lmc_img_myula_run_onchip") != 0) return -1;
   LMC_REQUIRE(pr != nullptr && io != nullptr, "lmc_img_myula_run_onchip: null descriptor");
   LMC_REQUIRE(lmc_img_myula_onchip_supported(pb, dtype),
-              "lmc_img_myula_run_onchip: needs LMC_F32, ny <= %d, nx <= %d, blur taps <= %d (use lmc_img_myula_run)",
-              OC_CL * 32, OC_W, OC_HB + 1);
+              "lmc_img_myula_run_onchip: needs LMC_F32, ny <= %d, nx <= %d, 5/6/7 blur taps on both axes "
+              "(use lmc_img_myula_run)", OC_CL * 32, OC_W);
   LMC_REQUIRE(C >= 0 && N >= 0, "lmc_img_myula_run_onchip: negative C or N");
   LMC_REQUIRE(pr->tau > 0 && pr->gamma > 0, "lmc_img_myula_run_onchip: tau and gamma must be positive");
   LMC_REQUIRE(pr->tv_niter >= 0 && pr->tv_sigma * pr->epsg * pr->gamma > 0,
@@ -549,10 +591,14 @@ extern "C" int lmc_img_myula_run_onchip(const lmc_img_problem* pb, const lmc_img
   A.a_x = (float)(1 - pr->tau / pr->gamma);
   A.tog = (float)(pr->tau / pr->gamma);
   A.s2t = (float)sqrt(2 * pr->tau);
-  const double tvg = pr->tv_sigma * (pr->epsg * pr->gamma);
-  A.tv_gamma = (float)tvg;
+  A.tv_gamma = (float)(pr->tv_sigma * (pr->epsg * pr->gamma));
   A.inv_g8 = (float)(1.0 / (8.0 * (double)A.tv_gamma));
   A.tv_niter = pr->tv_niter;
   A.tv_rtol = pr->tv_rtol;
-  return launch_onchip<32>(A, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (pb->ntap_y) {
+    case 5: return launch_onchip_nt<5>(A, st);
+    case 6: return launch_onchip_nt<6>(A, st);
+    default: return launch_onchip_nt<7>(A, st);
+  }
 }
