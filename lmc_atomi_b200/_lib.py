@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "_lmc_b200.so")
+LIB_PATH = os.environ.get("LMC_B200_LIB", os.path.join(HERE, "_lmc_b200.so"))
 
 MAX_COMP = 8
 F32, F64 = 0, 1

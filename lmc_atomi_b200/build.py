@@ -7,7 +7,9 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "_lmc_b200.so")
+# LMC_B200_LIB / LMC_NVCC_EXTRA: build (and load, see _lib.py) an experimental variant next to the default library
+OUT = os.environ.get("LMC_B200_LIB", os.path.join(HERE, "_lmc_b200.so"))
+EXTRA = os.environ.get("LMC_NVCC_EXTRA", "").split()
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-diag-suppress", "177"]
 
@@ -26,11 +28,12 @@ def build(force=False, verbose=False):
     nvcc = os.environ.get("NVCC", "nvcc")
     objs = []
     procs = []
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    bdir = os.path.join(HERE, "build", os.path.basename(OUT)[:-3])
+    os.makedirs(bdir, exist_ok=True)
     for s in srcs:
-        o = os.path.join(HERE, "build", os.path.basename(s)[:-3] + ".o")
+        o = os.path.join(bdir, os.path.basename(s)[:-3] + ".o")
         objs.append(o)
-        cmd = [nvcc, *NVCC_FLAGS, "-c", s, "-o", o] + (["-Xptxas", "-v"] if verbose else [])
+        cmd = [nvcc, *NVCC_FLAGS, *EXTRA, "-c", s, "-o", o] + (["-Xptxas", "-v"] if verbose else [])
         procs.append((cmd, subprocess.Popen(cmd)))
     for cmd, p in procs:
         if p.wait() != 0:

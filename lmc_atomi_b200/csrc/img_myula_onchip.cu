@@ -9,7 +9,7 @@
 //   pool : two (rr, ss) buffers of the TV dual field, RPC + 2 halo rows each; the
 //          second pair doubles as the scratch image of the blur passes
 //   BS   : `base` = everything of the MYULA update that does not depend on the TV prox
-// and in registers (thread = one column x a strip of RPC/2 rows): the pointwise
+// and in registers (thread = one column x a strip of RPC/OC_SPLIT rows): the pointwise
 // arrays p, q (current projected dual iterate).  Halo rows are PUSHED into the
 // neighbour CTA's shared memory (DSMEM) by the thread that produces them; the
 // per-chain TV objective is reduced across the cluster through 8 doubles per CTA.
@@ -41,11 +41,14 @@ constexpr int OC_W = 256;              // columns handled (nx <= OC_W)
 constexpr int OC_PADL = 8;             // zero columns left of column 0
 constexpr int OC_PITCH = OC_W + 16;    // floats per shared-memory row
 constexpr int OC_HB = 6;               // x halo rows per side (max blur taps - 1)
-constexpr int OC_NT = 512;             // threads per CTA: 256 columns x 2 row strips
+#ifndef OC_SPLIT
+#define OC_SPLIT 2
+#endif
+constexpr int OC_NT = OC_W * OC_SPLIT; // threads per CTA: 256 columns x OC_SPLIT row strips
 
 template <int RPC>
 struct OcLayout {
-  static constexpr int STRIP = RPC / 2;
+  static constexpr int STRIP = RPC / OC_SPLIT;
   static constexpr int XS_ROWS = RPC + 2 * OC_HB;
   static constexpr int DROWS = RPC + 2;             // halo row above, own rows, halo row below
   static constexpr int T_ROWS = RPC + 2 * OC_HB;    // blur scratch image (residual), local row a at T2 + a + OC_HB
@@ -109,6 +112,15 @@ __device__ __forceinline__ void oc_transpose4(float v[4], int m) {
   }
 }
 
+// split cluster barrier: everything stored before the arrive (shared memory of any CTA of the
+// cluster included) is visible to the cluster's threads after the matching wait
+__device__ __forceinline__ void oc_cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void oc_cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // Per-thread view of the CTA's shared memory and of the neighbours' windows.
 template <int RPC>
 struct OcCtx {
@@ -135,8 +147,8 @@ struct OcCtx {
 template <int RPC, bool FIRST, bool FULL>
 __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, int cur_ss, int nxt_rr, int nxt_ss,
                                               float cn, float gamma, float inv_g8,
-                                              float (&P)[RPC / 2], float (&Q)[RPC / 2]) {
-  constexpr int STRIP = RPC / 2;
+                                              float (&P)[RPC / OC_SPLIT], float (&Q)[RPC / OC_SPLIT]) {
+  constexpr int STRIP = RPC / OC_SPLIT;
   const int c = K.c, a0 = K.a0;
   double acc = 0.0;
   float accn = 0.0f, accd = 0.0f;
@@ -169,7 +181,7 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
     bool in, has_below;
     if (FULL) {
       in = true;
-      has_below = !(k == STRIP - 1 && K.h == 1 && last_cta);
+      has_below = !(k == STRIP - 1 && K.h == OC_SPLIT - 1 && last_cta);
     } else {
       in = K.colin && i < K.ny;
       has_below = i < K.ny - 1;
@@ -215,7 +227,7 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
         K.PL(nxt_rr + 0, c) = 0.0f;    // row -1 of the image
       }
     }
-    if (k == STRIP - 1 && K.h == 1) {  // last own row -> above-halo of the next CTA
+    if (k == STRIP - 1 && K.h == OC_SPLIT - 1) {  // last own row -> above-halo of the next CTA
       if (!last_cta) {
         K.pool_next[(nxt_rr + 0) * OC_PITCH + OC_PADL + c] = rrn;
       } else {
@@ -236,12 +248,29 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
 //   AB: x -> residual  (scratch image T2, rows [-hi_y, RPC - lo_y) of the CTA)
 //   CD: residual -> g on the thread's own strip, fused with the noise draw:
 //       base = (1 - tau/gamma) x - tau sigma_L2 g + sqrt(2 tau) xi      (algs.py:569)  -> BS
+// the observation rows a thread's residual rows need (issued early: the loads fly during sweep 0)
+template <int RPC, int NT, bool FULL>
+__device__ __forceinline__ void oc_load_b(const OcCtx<RPC>& K, const OcArgs& A, long long chain,
+                                          float (&bv)[(RPC + NT - 1 + OC_SPLIT - 1) / OC_SPLIT]) {
+  constexpr int TOT = RPC + NT - 1, HALF = (TOT + OC_SPLIT - 1) / OC_SPLIT;
+  const int hi_y = A.g.lo_y + NT - 1;
+  const float* bc = A.b + chain * A.b_stride;
+  const int j0 = K.h * HALF;
+#pragma unroll
+  for (int o = 0; o < HALF; ++o) {
+    const int i = K.r0 - hi_y + j0 + o;
+    const bool in = (FULL || K.colin) && i >= 0 && i < K.ny && j0 + o < TOT;
+    bv[o] = in ? __ldg(bc + (long long)i * K.nx + K.c) : 0.0f;
+  }
+}
+
 template <int RPC, int NT, bool FULL>
 __device__ __forceinline__ void oc_blur_base(const OcCtx<RPC>& K, const OcArgs& A, long long chain, long long n,
-                                             unsigned long long it_global) {
+                                             unsigned long long it_global,
+                                             const float (&bv)[(RPC + NT - 1 + OC_SPLIT - 1) / OC_SPLIT]) {
   using L = OcLayout<RPC>;
-  constexpr int STRIP = RPC / 2;
-  constexpr int TOT = RPC + NT - 1, HALF = (TOT + 1) / 2;
+  constexpr int STRIP = RPC / OC_SPLIT;
+  constexpr int TOT = RPC + NT - 1, HALF = (TOT + OC_SPLIT - 1) / OC_SPLIT;
   const Geom<float>& g = A.g;
   const int c = K.c, a0 = K.a0, r0 = K.r0, ny = K.ny, nx = K.nx;
   const int lo_y = g.lo_y, lo_x = g.lo_x, hi_y = lo_y + NT - 1;
@@ -256,7 +285,6 @@ __device__ __forceinline__ void oc_blur_base(const OcCtx<RPC>& K, const OcArgs& 
     const int j0 = K.h * HALF;
     const int aout0 = -hi_y + j0;          // first residual row of this thread
     const int rin0 = aout0 + lo_y;         // first x row it reads
-    const float* bc = A.b + chain * A.b_stride;
     const float* xrow = &K.XS(rin0, c + lo_x);
     float win[NT];
 #pragma unroll
@@ -273,10 +301,9 @@ __device__ __forceinline__ void oc_blur_base(const OcCtx<RPC>& K, const OcArgs& 
           float res = 0.0f;
           const bool in = FULL ? (i >= 0 && i < ny) : (K.colin && i >= 0 && i < ny);
           if (in) {
-            const float bv = __ldg(bc + (long long)i * nx + c);
 #pragma unroll
             for (int t = 0; t < NT; ++t) res = fmaf(wy[t], win[(o + t) % NT], res);
-            res -= bv;
+            res -= bv[o];
           }
           K.PL(L::T2 + a + OC_HB, c) = res;
         }
@@ -289,6 +316,7 @@ __device__ __forceinline__ void oc_blur_base(const OcCtx<RPC>& K, const OcArgs& 
     const int rin0 = a0 - hi_y;
     const float* rrow = &K.PL(L::T2 + rin0 + OC_HB, c - lo_x);
     const int quads_per_row = (nx + 3) / 4;
+    const float* nz = A.noise != nullptr ? A.noise + (chain * A.N + n) * g.P + (long long)r0 * nx + c : nullptr;
     float win[NT];
     float z[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
@@ -299,7 +327,7 @@ __device__ __forceinline__ void oc_blur_base(const OcCtx<RPC>& K, const OcArgs& 
       win[jj % NT] = u;
       if (jj >= NT - 1) {
         const int k = jj - (NT - 1), a = a0 + k, i = r0 + a;
-        if ((k & 3) == 0 && A.noise == nullptr) {
+        if ((k & 3) == 0 && nz == nullptr) {
           const int m = c & 3;
           img_noise4<float>(A.key, A.chain_offset + (unsigned long long)chain, it_global, i + m, c >> 2,
                             quads_per_row, z);
@@ -309,8 +337,7 @@ __device__ __forceinline__ void oc_blur_base(const OcCtx<RPC>& K, const OcArgs& 
 #pragma unroll
         for (int t = 0; t < NT; ++t) gv = fmaf(wy[t], win[(k + NT - 1 - t) % NT], gv);
         float xi = z[k & 3];
-        if (A.noise != nullptr && K.colin && i < ny)
-          xi = __ldg(A.noise + (chain * A.N + n) * g.P + (long long)i * nx + c);
+        if (nz != nullptr && K.colin && i < ny) xi = __ldg(nz + (long long)a * nx);
         K.BS(a) = A.a_x * K.XS(a, c) - A.tau * (A.sigma_l2 * gv) + A.s2t * xi;
       }
     }
@@ -359,7 +386,7 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
     // ---- load x (own rows + blur halo rows straight from HBM; zero outside the image)
     {
       const float* xc = A.x + chain * g.P;
-      for (int a = -OC_HB + h; a < RPC + OC_HB; a += 2) {
+      for (int a = -OC_HB + h; a < RPC + OC_HB; a += OC_SPLIT) {
         const int i = r0 + a;
         float v = 0.0f;
         if (i >= 0 && i < ny && K.colin) v = xc[(long long)i * nx + c];
@@ -370,6 +397,8 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
 
     for (long long n = 0; n < A.N; ++n) {
       float P[STRIP], Q[STRIP];
+      float bv[(RPC + NT - 1 + OC_SPLIT - 1) / OC_SPLIT];
+      oc_load_b<RPC, NT, FULL>(K, A, chain, bv);
       double prev_obj = 0.0;
       int kf = 0;
       const unsigned long long it_global = A.iter_offset + (unsigned long long)n;
@@ -389,7 +418,7 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
         acc = lmc_warp_sum(acc);
         if (lane == 0) red[wid] = acc;
         // the data-term gradient does not depend on the TV loop: it runs between sweep 0 and its barrier
-        if (it == 0) oc_blur_base<RPC, NT, FULL>(K, A, chain, n, it_global);
+        if (it == 0) oc_blur_base<RPC, NT, FULL>(K, A, chain, n, it_global, bv);
         __syncthreads();    // red[] complete (and, on sweep 0, the scratch reads are done)
         if (tid < OC_CL) {
           double s = 0.0;
@@ -442,6 +471,9 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
             if (a >= RPC - OC_HB && rank < OC_CL - 1) K.xs_next[(a - RPC + OC_HB) * OC_PITCH + OC_PADL + c] = xn[k];
           }
         }
+        // x (own rows + pushed halo rows) is complete: arrive now, let the statistics traffic to HBM
+        // overlap the barrier latency, wait afterwards
+        oc_cluster_arrive();
         if (K.colin && A.samples != nullptr) {
           float* sp = A.samples + (chain * A.N + n) * g.P + o0;
 #pragma unroll
@@ -469,7 +501,7 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
           }
         }
       }
-      cluster.sync();   // new x (own rows + halo rows) visible; dual buffers free for the next iteration
+      oc_cluster_wait();   // new x (own rows + halo rows) visible; dual buffers free for the next iteration
     }
 
     // ---- store the chain state

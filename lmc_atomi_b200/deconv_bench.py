@@ -56,7 +56,12 @@ def _time_launches(torch, dev, fn, steps, warmup):
     return a.elapsed_time(b) * 1e-3 / steps
 
 
-def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dtype="float32"):
+# measured once per round with `ncu --set full` (profiles/): dram__bytes_read+write per launch of the
+# on-chip kernel divided by the chain-iterations of that launch (256 chains x 10 iterations, 256x256)
+ONCHIP_DRAM_BYTES_PER_CHAIN_ITER = (134.6e6 + 86.6e6) / 2560.0
+
+
+def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dtype="float32", engine="auto"):
     import torch
     _, eng = make_engine(dims, dev, dtype)
     L = 1.0 / SIGMA ** 2
@@ -68,7 +73,7 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
 
     def launch():
         state["keep"] = eng.myula(x, iters, tau, gamma, TAU_REG, 10, 1e-4, seed=0, mean=mean,
-                                  iter_offset=state["it"])
+                                  iter_offset=state["it"], stat_count0=state["it"], engine=engine)
         state["it"] += iters
 
     for _ in range(2):      # burn-in so that the TV early exit is in its steady regime
@@ -84,13 +89,29 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     bpp = roofline.myula_bytes_per_pixel(j, item)
     peaks = roofline.measured_peaks()
     ach = bpp * P * chains * iters / secs / 1e9
-    return {"metric": "myula_deconv_chain_iters_per_sec", "value": chains * iters / secs, "unit": "chain-iters/s",
-            "pixel_iters_per_sec": chains * iters * P / secs, "dtype": dtype, "dims": list(dims), "chains": chains,
-            "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "tv_sweeps_per_iter": j,
-            "state_bytes": int(10 * chains * P * item), "l2_policy": "per-chain arrays total far more than the 126 MB L2",
-            "roofline": {"bound": "hbm", "kernel": "img_myula_kernel<%s>" % ("float" if item == 4 else "double"),
-                         "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
-                         "bytes_per_pixel_iter": bpp, "traffic": None, "peak_source": peaks["source"]}}
+    onchip = engine == "onchip" or (engine == "auto" and eng.onchip_supported())
+    if onchip:
+        kernel = "img_myula_onchip_kernel<32,5,%d>" % (1 if dims == (256, 256) else 0)
+        policy = ("chain state resident in the shared memory of an 8-CTA cluster for all iterations of a launch; "
+                  "%d chains per launch, state of the batch (x + mean) %.0f MB >> 126 MB L2 only for the start/end "
+                  "load/store" % (chains, 2 * chains * P * item / 1e6))
+        traffic = ONCHIP_DRAM_BYTES_PER_CHAIN_ITER * chains * iters if dims == (256, 256) else None
+        note = ("roofline kept as the HBM bound of the streaming formulation ((12+9j) x 4 B per pixel-iteration); "
+                "the on-chip kernel removes that traffic (see `traffic`, measured DRAM bytes per launch), so frac can "
+                "exceed 1 and the binding resource is instruction issue (smsp__issue_active in profiles/)")
+    else:
+        kernel = "img_myula_kernel<%s>" % ("float" if item == 4 else "double")
+        policy, traffic, note = "per-chain arrays total far more than the 126 MB L2", None, None
+    out = {"metric": "myula_deconv_chain_iters_per_sec", "value": chains * iters / secs, "unit": "chain-iters/s",
+           "pixel_iters_per_sec": chains * iters * P / secs, "dtype": dtype, "dims": list(dims), "chains": chains,
+           "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "tv_sweeps_per_iter": j,
+           "engine": "onchip" if onchip else "stream", "state_bytes": int(10 * chains * P * item), "l2_policy": policy,
+           "roofline": {"bound": "hbm", "kernel": kernel,
+                        "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
+                        "bytes_per_pixel_iter": bpp, "traffic": traffic, "peak_source": peaks["source"]}}
+    if note:
+        out["roofline"]["note"] = note
+    return out
 
 
 def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtype="float32"):
@@ -129,5 +150,8 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
 
 def run(dev, steps=3, warmup=3, **kw):
     out = run_myula(dev, steps=steps, warmup=warmup, **kw)
+    # the general / fp64-validation path, for comparison
+    st = run_myula(dev, steps=max(1, min(steps, 2)), warmup=1, engine="stream", **kw)
+    out["streaming_kernel"] = {k: st[k] for k in ("value", "unit", "ms_per_launch", "tv_sweeps_per_iter", "roofline")}
     out["ulpda"] = run_ulpda(dev, steps=max(1, min(steps, 3)), warmup=min(warmup, 2))
     return out
