@@ -105,6 +105,9 @@ SIGNATURES = {
                                            C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),
     "lmc_img_ulpda_run": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgUlpdaParams), C.c_int, C.c_int64,
                                     C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),
+    "lmc_img_ulpda_band_supported": (C.c_int, [C.POINTER(ImgProblem), C.c_int]),
+    "lmc_img_ulpda_run_band": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgUlpdaParams), C.c_int, C.c_int64,
+                                         C.c_int64, C.c_uint64, C.c_uint64, C.c_int64, C.POINTER(ImgIo), C.c_void_p]),
     "lmc_img_blur": (C.c_int, [C.POINTER(ImgProblem), C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,
                                C.c_void_p]),
     "lmc_img_grad": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,

@@ -3,21 +3,65 @@
 
 namespace {
 
+constexpr int BAND_RB = 16;   // rows per band
+
 template <typename real>
 size_t ulpda_ws_bytes(int ny, int nx, long long C) {
   const size_t P = (size_t)ny * nx;
-  const size_t tiles = (size_t)((ny + TH - 1) / TH) * ((nx + TW - 1) / TW);
+  size_t tiles = (size_t)((ny + TH - 1) / TH) * ((nx + TW - 1) / TW);
+  const size_t bands = (size_t)(ny + BAND_RB - 1) / BAND_RB;   // the band kernel keeps one partial per band
+  if (bands > tiles) tiles = bands;
   return 256 + align_up(C * sizeof(LsqrState)) + align_up((size_t)3 * C * tiles * sizeof(double)) +
          4 * align_up((size_t)C * P * sizeof(real)) /* optb, u, v, w */;
 }
 
 template <typename real>
+bool band_supported(const lmc_img_problem* pb) {
+  if (pb->ntap_y != pb->ntap_x || pb->ntap_y < 5 || pb->ntap_y > 7) return false;   // H5 / H6 / H7
+  const size_t smem = Band<real, 7, BAND_RB>::smem_bytes(band_pitch(pb->nx));
+  return smem <= 200 * 1024;
+}
+
+template <typename real, int NT>
+int launch_band(UlpdaArgs<real>& A, cudaStream_t st) {
+  const size_t smem = Band<real, NT, BAND_RB>::smem_bytes(A.pitch);
+  auto kern = img_ulpda_band_kernel<real, NT, BAND_RB>;
+  int dev = 0, sms = 0, occ = 0;
+  LMC_CUDA_OK(cudaGetDevice(&dev));
+  LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  LMC_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  LMC_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, BAND_BT, smem));
+  LMC_REQUIRE(occ >= 1, "ULPDA band kernel does not fit on an SM (smem %zu)", smem);
+  const long long cap = (long long)sms * occ;
+  const long long g = A.group < A.C ? A.group : A.C;
+  const long long items = g * A.g.tiles;
+  int grid = (int)(items < cap ? items : cap);
+  if (grid < 1) grid = 1;
+  void* kargs[] = {(void*)&A};
+  LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(BAND_BT), kargs, smem, st));
+  return 0;
+}
+
+template <typename real>
 int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long long C, long long N, uint64_t seed,
               uint64_t chain_offset, const lmc_img_io* io, int mode, const void* prox_in, void* prox_out,
-              cudaStream_t st) {
+              cudaStream_t st, bool band = false, long long group = 0) {
   UlpdaArgs<real> A;
   memset(&A, 0, sizeof(A));
   fill_geom(pb, A.g);
+  if (band) {   // one partial per band of BAND_RB rows
+    A.g.tiles_x = 1;
+    A.g.tiles_y = (pb->ny + BAND_RB - 1) / BAND_RB;
+    A.g.tiles = A.g.tiles_y;
+    A.pitch = band_pitch(pb->nx);
+    if (group <= 0) {
+      // LSQR vectors u, v, w, z of a group stay L2 resident (about 3/4 of the 126 MB L2)
+      const double per_chain = 4.0 * (double)A.g.P * sizeof(real);
+      group = (long long)(96.0 * 1024 * 1024 / per_chain);
+      if (group < 1) group = 1;
+    }
+    A.group = group < C ? group : C;
+  }
   const size_t need = ulpda_ws_bytes<real>(pb->ny, pb->nx, C);
   LMC_REQUIRE(io->d_workspace != nullptr && io->workspace_bytes >= need, "image workspace too small (%zu < %zu)",
               io->workspace_bytes, need);
@@ -75,6 +119,13 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
     A.out = (real*)prox_out;
   }
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
+  if (band) {
+    switch (pb->ntap_y) {
+      case 5: return launch_band<real, 5>(A, st);
+      case 6: return launch_band<real, 6>(A, st);
+      default: return launch_band<real, 7>(A, st);
+    }
+  }
   return launch_persistent(img_ulpda_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);
 }
 
@@ -101,6 +152,34 @@ extern "C" int lmc_img_ulpda_run(const lmc_img_problem* pb, const lmc_img_ulpda_
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64 ? run_ulpda<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st)
                           : run_ulpda<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st);
+}
+
+extern "C" int lmc_img_ulpda_band_supported(const lmc_img_problem* pb, int dtype) {
+  if (pb == nullptr || pb->ny < 1 || pb->nx < 1) return 0;
+  if (dtype == LMC_F32) return band_supported<float>(pb) ? 1 : 0;
+  if (dtype == LMC_F64) return band_supported<double>(pb) ? 1 : 0;
+  return 0;
+}
+
+extern "C" int lmc_img_ulpda_run_band(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, int dtype, int64_t C,
+                                      int64_t N, uint64_t seed, uint64_t chain_offset, int64_t group,
+                                      const lmc_img_io* io, void* stream) {
+  if (check_problem(pb, "lmc_img_ulpda_run_band") != 0) return -1;
+  LMC_REQUIRE(pr != nullptr && io != nullptr, "lmc_img_ulpda_run_band: null descriptor");
+  LMC_REQUIRE(lmc_img_ulpda_band_supported(pb, dtype),
+              "lmc_img_ulpda_run_band: needs 5/6/7 blur taps on both axes and a row that fits in shared memory "
+              "(use lmc_img_ulpda_run)");
+  LMC_REQUIRE(C >= 0 && N >= 0, "lmc_img_ulpda_run_band: negative C or N");
+  LMC_REQUIRE(pr->tau > 0 && pr->mu > 0 && pr->g_sigma > 0, "lmc_img_ulpda_run_band: tau, mu, g_sigma must be positive");
+  if (C == 0 || N == 0) return 0;
+  LMC_REQUIRE(io->d_x && io->d_xhat && io->d_y && io->d_warm && pb->d_b,
+              "lmc_img_ulpda_run_band: d_x, d_xhat, d_y, d_warm and d_b are required");
+  LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
+              "lmc_img_ulpda_run_band: b_chain_stride must be 0 or ny*nx");
+  cudaStream_t st = (cudaStream_t)stream;
+  return dtype == LMC_F64
+             ? run_ulpda<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true, group)
+             : run_ulpda<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true, group);
 }
 
 extern "C" int lmc_img_l2_prox(const lmc_img_problem* pb, int dtype, double tau, int32_t iter_lim, double atol,

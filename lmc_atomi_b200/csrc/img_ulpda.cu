@@ -64,6 +64,9 @@ struct UlpdaArgs {
   int isotropic, gfirst, iter_lim, warm_on;
   double atol, btol, ctol;
   int mode;  // 0 = ULPDA, 1 = L2 prox only
+  // band kernel only (img_ulpda_band.inl)
+  int pitch;        // shared-memory row pitch in elements
+  long long group;  // chains advanced together (working set kept near the L2 size)
 };
 
 __device__ __forceinline__ void sym_ortho(double a, double b, double& c, double& s, double& r) {
@@ -191,15 +194,16 @@ __device__ __forceinline__ double chain_partial(const UlpdaArgs<real>& A, int q,
   return lmc_warp_sum(s);
 }
 
+// one warp per chain of [c_lo, c_hi) (c_lo, c_hi: arguments of the enclosing scalar phase)
 #define LMC_FOR_CHAINS_BY_WARP(chain)                                                   \
   const int lane = threadIdx.x & 31;                                                    \
-  const long long warp_ = ((long long)blockIdx.x * NTHREADS + threadIdx.x) >> 5;        \
-  const long long nwarps_ = ((long long)gridDim.x * NTHREADS) >> 5;                     \
-  for (long long chain = warp_; chain < A.C; chain += nwarps_)
+  const long long warp_ = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;      \
+  const long long nwarps_ = ((long long)gridDim.x * blockDim.x) >> 5;                   \
+  for (long long chain = c_lo + warp_; chain < c_hi; chain += nwarps_)
 
 // ---------------------------------------------------------------- S1
 template <typename real>
-__device__ void phase_s1(const UlpdaArgs<real>& A) {
+__device__ void phase_s1(const UlpdaArgs<real>& A, long long c_lo, long long c_hi) {
   LMC_FOR_CHAINS_BY_WARP(chain) {
     double sb = chain_partial(A, 0, chain, lane), su = chain_partial(A, 1, chain, lane);
     if (lane == 0) {
@@ -249,7 +253,7 @@ __device__ void phase_v0(const UlpdaArgs<real>& A, real* smem, double* red) {
 
 // ---------------------------------------------------------------- S2
 template <typename real>
-__device__ void phase_s2(const UlpdaArgs<real>& A) {
+__device__ void phase_s2(const UlpdaArgs<real>& A, long long c_lo, long long c_hi) {
   LMC_FOR_CHAINS_BY_WARP(chain) {
     LsqrState s = A.st[chain];
     if (!s.active) continue;
@@ -316,7 +320,7 @@ __device__ void phase_ka(const UlpdaArgs<real>& A, real* smem, double* red) {
 
 // ---------------------------------------------------------------- Sa
 template <typename real>
-__device__ void phase_sa(const UlpdaArgs<real>& A) {
+__device__ void phase_sa(const UlpdaArgs<real>& A, long long c_lo, long long c_hi) {
   LMC_FOR_CHAINS_BY_WARP(chain) {
     LsqrState s = A.st[chain];
     if (!s.active) continue;
@@ -369,7 +373,7 @@ __device__ void phase_kb(const UlpdaArgs<real>& A, real* smem, double* red) {
 
 // ---------------------------------------------------------------- Sb: scipy lsqr scalar block
 template <typename real>
-__device__ void phase_sb(const UlpdaArgs<real>& A) {
+__device__ void phase_sb(const UlpdaArgs<real>& A, long long c_lo, long long c_hi) {
   const double eps = 2.220446049250313e-16;
   LMC_FOR_CHAINS_BY_WARP(chain) {
     LsqrState s = A.st[chain];
@@ -539,22 +543,22 @@ __global__ void __launch_bounds__(NTHREADS) img_ulpda_kernel(const __grid_consta
     if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
     phase_primal_init(A, smem, red);
     grid.sync();
-    phase_s1(A);
+    phase_s1(A, 0, A.C);
     grid.sync();
     phase_v0(A, smem, red);
     grid.sync();
-    phase_s2(A);
+    phase_s2(A, 0, A.C);
     grid.sync();
     while (*(volatile int*)A.n_active != 0) {
       grid.sync();   // everyone has read n_active before it is reset
       if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
       phase_ka(A, smem, red);
       grid.sync();
-      phase_sa(A);
+      phase_sa(A, 0, A.C);
       grid.sync();
       phase_kb(A, smem, red);
       grid.sync();
-      phase_sb(A);
+      phase_sb(A, 0, A.C);
       grid.sync();
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(A.counters + 2, (unsigned long long)A.C);
@@ -569,4 +573,5 @@ __global__ void __launch_bounds__(NTHREADS) img_ulpda_kernel(const __grid_consta
 
 }  // namespace
 
+#include "img_ulpda_band.inl"
 #include "img_host_ulpda.inl"

@@ -114,7 +114,7 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     return out
 
 
-def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtype="float32"):
+def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtype="float32", engine="auto", group=0):
     import torch
     _, eng = make_engine(dims, dev, dtype)
     L = 1.0 / SIGMA ** 2
@@ -126,7 +126,8 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
 
     def launch():
         state["keep"] = eng.ulpda(x, xhat, y, warm, iters, tau, mu, 1.0, TAU_REG, True, False, 50, seed=0,
-                                  mean=mean, iter_offset=state["it"])
+                                  mean=mean, iter_offset=state["it"], stat_count0=state["it"], engine=engine,
+                                  group=group)
         state["it"] += iters
 
     for _ in range(3):
@@ -143,7 +144,11 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
     return {"metric": "ulpda_deconv_chain_iters_per_sec", "value": chains * iters / secs, "unit": "chain-iters/s",
             "pixel_iters_per_sec": chains * iters * P / secs, "dtype": dtype, "dims": list(dims), "chains": chains,
             "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "lsqr_iters_per_solve": k,
-            "roofline": {"bound": "hbm", "kernel": "img_ulpda_kernel<%s>" % ("float" if item == 4 else "double"),
+            "engine": "band" if (engine == "band" or (engine == "auto" and eng.band_supported())) else "tile",
+            "group": group,
+            "roofline": {"bound": "hbm", "kernel": ("img_ulpda_band_kernel<%s,5,16>" if (
+                engine == "band" or (engine == "auto" and eng.band_supported())) else "img_ulpda_kernel<%s>") % (
+                "float" if item == 4 else "double"),
                          "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
                          "bytes_per_pixel_iter": bpp, "traffic": None, "peak_source": peaks["source"]}}
 

@@ -302,8 +302,12 @@ class DeconvEngine:
     def ulpda(self, x, xhat, y, warm, N, tau, mu, theta=1.0, g_sigma=1.0, isotropic=True, gfirst=True,
               lsqr_iter_lim=50, warm_start=True, atol=1e-6, btol=1e-6, conlim=1e8, z=None, seed=0,
               chain_offset=0, noise=None, samples=None, ysamples=None, mean=None, m2=None, burnin=0,
-              stat_count0=0, iter_offset=0):
-        """Advances (x, xhat, y, warm) in place by N ULPDA iterations (algs.py:432-467)."""
+              stat_count0=0, iter_offset=0, engine="auto", group=0):
+        """Advances (x, xhat, y, warm) in place by N ULPDA iterations (algs.py:432-467).
+
+        ``engine``: "band" = row-band kernel (fused two-pass blur, chains advanced in L2-sized groups of
+        ``group`` chains, 0 = automatic), "tile" = 32x32-tile kernel (any separable filter), "auto" = band
+        when it applies.  Both are CUDA; there is no CPU path."""
         torch, lib = self.torch, self.lib
         Cn = x.shape[0]
         pr = _lib.ImgUlpdaParams()
@@ -322,11 +326,25 @@ class DeconvEngine:
             io.d_z = zt.data_ptr()
         io.d_ysamples = ysamples.data_ptr() if ysamples is not None else None
         pb = self._problem()
+        if engine not in ("auto", "band", "tile"):
+            raise ValueError("engine must be 'auto', 'band' or 'tile'")
+        band = engine == "band" or (engine == "auto" and self.band_supported())
         with torch.cuda.device(self.dev):
-            rc = lib.lmc_img_ulpda_run(C.byref(pb), C.byref(pr), _dt(self.dtype), Cn, int(N), seed & (2 ** 64 - 1),
-                                       int(chain_offset), C.byref(io), _stream(torch, self.dev))
-        _lib.check(rc, "lmc_img_ulpda_run")
+            if band:
+                rc = lib.lmc_img_ulpda_run_band(C.byref(pb), C.byref(pr), _dt(self.dtype), Cn, int(N),
+                                                seed & (2 ** 64 - 1), int(chain_offset), int(group), C.byref(io),
+                                                _stream(torch, self.dev))
+            else:
+                rc = lib.lmc_img_ulpda_run(C.byref(pb), C.byref(pr), _dt(self.dtype), Cn, int(N),
+                                           seed & (2 ** 64 - 1), int(chain_offset), C.byref(io),
+                                           _stream(torch, self.dev))
+        _lib.check(rc, "lmc_img_ulpda_run_band" if band else "lmc_img_ulpda_run")
         return ws, nz, zt
+
+    def band_supported(self):
+        """True when the row-band ULPDA kernel (csrc/img_ulpda_band.inl) covers this problem."""
+        pb = self._problem()
+        return bool(self.lib.lmc_img_ulpda_band_supported(C.byref(pb), _dt(self.dtype)))
 
     # ------------------------------------------------------------------ L2 prox (LSQR)
     def l2_prox(self, x, tau, warm, iter_lim=50, atol=1e-6, btol=1e-6, conlim=1e8):
@@ -364,7 +382,8 @@ class DeconvEngine:
         return st
 
     def run_ulpda(self, chains, N, tau, mu, theta=1.0, g_sigma=1.0, isotropic=True, gfirst=False, lsqr_iter_lim=50,
-                  seed=0, chain_offset=0, burnin=0, x0=None, second_moment=True, sync=True) -> ImageStats:
+                  seed=0, chain_offset=0, burnin=0, x0=None, second_moment=True, sync=True, engine="auto",
+                  group=0) -> ImageStats:
         torch = self.torch
         x = self._buf(x0, chains)
         xhat = x.clone()
@@ -373,7 +392,8 @@ class DeconvEngine:
         mean = torch.zeros((chains, self.P), dtype=self.tdt, device=self.dev)
         m2 = torch.zeros_like(mean) if second_moment else None
         keep = self.ulpda(x, xhat, y, warm, N, tau, mu, theta, g_sigma, isotropic, gfirst, lsqr_iter_lim,
-                          seed=seed, chain_offset=chain_offset, mean=mean, m2=m2, burnin=burnin)
+                          seed=seed, chain_offset=chain_offset, mean=mean, m2=m2, burnin=burnin, engine=engine,
+                          group=group)
         if sync:
             torch.cuda.current_stream(self.dev).synchronize()
             keep = None

@@ -16,5 +16,7 @@ torch.cuda.set_device(dev)
 if which == "myula":
     r = deconv_bench.run_myula(dev, steps=2, warmup=1, chains=chains, iters=iters)
 else:
-    r = deconv_bench.run_ulpda(dev, steps=2, warmup=1, chains=chains, iters=iters)
+    engine = sys.argv[4] if len(sys.argv) > 4 else "auto"
+    group = int(sys.argv[5]) if len(sys.argv) > 5 else 0
+    r = deconv_bench.run_ulpda(dev, steps=2, warmup=1, chains=chains, iters=iters, engine=engine, group=group)
 print(json.dumps(r))

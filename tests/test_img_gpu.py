@@ -176,9 +176,10 @@ def test_myula_trajectory_fp64(torch, dims, kernel):
     assert eng.read_counters()["tv_sweeps"] == sum(min(u + 1, 10) for u in tv.updates)
 
 
+@pytest.mark.parametrize("engine", ["tile", "band"])
 @pytest.mark.parametrize("dims,kernel,iso,gfirst", [((64, 64), 5, True, False), ((40, 52), 5, False, False),
                                                     ((33, 95), 6, True, True), ((64, 64), 7, True, False)])
-def test_ulpda_trajectory_fp64(torch, dims, kernel, iso, gfirst):
+def test_ulpda_trajectory_fp64(torch, dims, kernel, iso, gfirst, engine):
     from lmc_atomi_b200 import imaging as I
     from oracle import deconv_ref as D
     N = 12
@@ -194,7 +195,7 @@ def test_ulpda_trajectory_fp64(torch, dims, kernel, iso, gfirst):
     x, xhat, y, warm = z(1, P), z(1, P), z(1, 2, P), z(1, P)
     samples, ys = z(1, N, P), z(1, N, 2, P)
     eng.ulpda(x, xhat, y, warm, N, pb["tau0"], pb["mu0"], 1.0, 0.3, iso, gfirst, 50, noise=noise[None],
-              samples=samples, ysamples=ys)
+              samples=samples, ysamples=ys, engine=engine)
     got = samples.cpu().numpy()[0]
     errs = [rel(got[n], want[n]) for n in range(N)]
     assert max(errs) < 1e-11, errs
@@ -224,7 +225,8 @@ def test_myula_fp32_within_tolerance(torch, engine):
     assert err < 1e-5
 
 
-def test_ulpda_fp32_within_tolerance(torch):
+@pytest.mark.parametrize("engine", ["tile", "band"])
+def test_ulpda_fp32_within_tolerance(torch, engine):
     from lmc_atomi_b200 import imaging as I
     from oracle import deconv_ref as D
     dims, N = (64, 64), 12
@@ -237,10 +239,10 @@ def test_ulpda_fp32_within_tolerance(torch):
     z = lambda *s: torch.zeros(s, dtype=torch.float32, device="cuda")
     x, xhat, y, warm, samples = z(1, P), z(1, P), z(1, 2, P), z(1, P), z(1, N, P)
     eng.ulpda(x, xhat, y, warm, N, pb["tau0"], pb["mu0"], 1.0, 0.3, True, False, 50, noise=noise[None],
-              samples=samples)
+              samples=samples, engine=engine)
     got = samples.cpu().numpy()[0]
     err = max(rel(got[n], want[n]) for n in range(N))
-    print(f"ULPDA fp32 free-run rel err over {N} iterations: {err:.3e}")
+    print(f"ULPDA fp32 ({engine}) free-run rel err over {N} iterations: {err:.3e}")
     # LSQR stops on atol=btol=1e-6: the solve itself is only 1e-6-accurate, so fp32 rounding can move
     # the stopping iteration; the tolerance reflects the solver's own accuracy.
     assert err < 2e-5
@@ -271,3 +273,29 @@ def test_batched_chains_are_independent(torch):
         want = D.UnadjustedLangevinPrimalDual(pb["l2"](), pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"],
                                               theta=1., niter=N, gfirst=False, noise=noise[c])
         assert rel(got[c], want) < 1e-11
+
+
+def test_ulpda_band_groups_match_tile_kernel(torch):
+    """Band kernel with chain groups smaller than the batch (each group runs all N iterations before the
+    next) == tile kernel advancing all chains in lockstep; in-kernel Philox noise, running statistics."""
+    from lmc_atomi_b200 import imaging as I
+    dims, N, Cn = (70, 96), 6, 5
+    pb = _problem(dims)
+    P = dims[0] * dims[1]
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    assert eng.band_supported()
+    out = {}
+    for engine, group in (("tile", 0), ("band", 2), ("band", 0)):
+        z = lambda *s: torch.zeros(s, dtype=torch.float64, device="cuda")
+        x, xhat, y, warm, mean, m2 = z(Cn, P), z(Cn, P), z(Cn, 2, P), z(Cn, P), z(Cn, P), z(Cn, P)
+        eng.counters.zero_()
+        eng.ulpda(x, xhat, y, warm, N, pb["tau0"], pb["mu0"], 1.0, 0.3, True, False, 50, seed=5, chain_offset=77,
+                  mean=mean, m2=m2, burnin=1, engine=engine, group=group)
+        torch.cuda.synchronize()
+        out[(engine, group)] = [t.cpu().numpy() for t in (x, xhat, y, warm, mean, m2)] + [eng.read_counters()]
+    ref = out[("tile", 0)]
+    for key in (("band", 2), ("band", 0)):
+        for a, b in zip(out[key][:6], ref[:6]):
+            assert rel(a, b) < 1e-11, key
+        assert out[key][6] == ref[6], key           # same LSQR iteration counts
+    assert np.abs(ref[0]).max() > 10
