@@ -38,31 +38,56 @@ __device__ __forceinline__ double band_block_sum(double v, double* red) {
   return s;
 }
 
-// rows [i0 + r0, i0 + r0 + rows) of scale * src -> S (zero outside the image)
+// rows [ifirst, ifirst + rows) of src -> S (zero outside the image), as 16-byte cp.async copies when the
+// rows are 16-byte aligned.  Ends with the data visible to the whole CTA.
 template <typename real>
 __device__ __forceinline__ void band_stage(real* S, int pitch, const real* __restrict__ src, int ny, int nx, int ifirst,
-                                           int rows, real scale) {
+                                           int rows) {
+  constexpr int EPV = 16 / sizeof(real);
+  const bool vec = (nx % EPV == 0) && ((reinterpret_cast<size_t>(src) & 15) == 0);
   for (int r = 0; r < rows; ++r) {
     const int i = ifirst + r;
     real* dst = S + r * pitch + BAND_PAD;
     if (i >= 0 && i < ny) {
       const real* s = src + (long long)i * nx;
-      for (int c = threadIdx.x; c < nx; c += BAND_BT) dst[c] = scale * s[c];
+      if (vec) {
+        for (int c = threadIdx.x * EPV; c < nx; c += BAND_BT * EPV) {
+          const unsigned d = (unsigned)__cvta_generic_to_shared(dst + c);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(s + c) : "memory");
+        }
+      } else {
+        for (int c = threadIdx.x; c < nx; c += BAND_BT) dst[c] = s[c];
+      }
     } else {
       for (int c = threadIdx.x; c < nx; c += BAND_BT) dst[c] = real(0);
     }
   }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
 }
 
-// second half of the operator: T (rows i0 - hi_y .. of a row-masked image) -> H^T T on the band,
-// epi(i, c, k, value) for every in-image output pixel (k = row within the band)
-template <typename real, int NT, int RB, class Epi>
+// second half of the operator: T (rows i0 - hi_y .. of a row-masked image) -> H^T T on the band.
+// pre(i, c, v) loads the NPRE global operands of pixel (i, c) of the phase's pointwise update; they are
+// fetched PFD rows ahead (all loads of a block in flight together), epi(i, c, k, value, v) consumes them
+// (k = row within the band).  Both only for in-image pixels.
+template <typename real, int NT, int RB, int NPRE, int PFD, class Pre, class Epi>
 __device__ __forceinline__ void band_adjoint(const Geom<real>& g, const real* T, int pitch, int i0, const real (&wx)[NT],
-                                             const real (&wy)[NT], Epi&& epi) {
+                                             const real (&wy)[NT], Pre&& pre, Epi&& epi) {
+  static_assert(RB % PFD == 0, "prefetch depth must divide the band height");
+  constexpr int NBLK = RB / PFD;
   const int lox = g.lo_x;
   for (int c = threadIdx.x; c < g.nx; c += BAND_BT) {
     const real* trow = T + BAND_PAD + c - lox;
     real win[NT];
+    real pf[2][PFD][NPRE > 0 ? NPRE : 1];   // two blocks of PFD rows in flight
+    if (NPRE > 0) {
+#pragma unroll
+      for (int bl = 0; bl < 2 && bl < NBLK; ++bl)
+#pragma unroll
+        for (int kk = 0; kk < PFD; ++kk)
+          if (i0 + bl * PFD + kk < g.ny) pre(i0 + bl * PFD + kk, c, pf[bl][kk]);
+    }
 #pragma unroll
     for (int jj = 0; jj < RB + NT - 1; ++jj) {
       real u = real(0);
@@ -74,7 +99,12 @@ __device__ __forceinline__ void band_adjoint(const Geom<real>& g, const real* T,
         real gv = real(0);
 #pragma unroll
         for (int t = 0; t < NT; ++t) gv = Math<real>::fma(wy[t], win[(k + NT - 1 - t) % NT], gv);
-        if (i < g.ny) epi(i, c, k, gv);
+        if (i < g.ny) epi(i, c, k, gv, pf[(k / PFD) & 1][k % PFD]);
+        if (NPRE > 0 && (k % PFD) == PFD - 1 && k / PFD + 2 < NBLK) {   // block consumed: fetch block + 2 into its slot
+#pragma unroll
+          for (int kk = 0; kk < PFD; ++kk)
+            if (i0 + k + 1 + PFD + kk < g.ny) pre(i0 + k + 1 + PFD + kk, c, pf[(k / PFD) & 1][kk]);
+        }
       }
     }
   }
@@ -133,12 +163,12 @@ __device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real (&wx)
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     __syncthreads();
-    band_stage(T, pitch, A.b + chain * A.b_stride, g.ny, g.nx, i0 - hi_y, Band<real, NT, RB>::TROWS, real(1));
-    __syncthreads();
+    band_stage(T, pitch, A.b + chain * A.b_stride, g.ny, g.nx, i0 - hi_y, Band<real, NT, RB>::TROWS);
     real* ob = A.optb + chain * g.P;
-    band_adjoint<real, NT, RB>(g, T, pitch, i0, wx, wy, [&](int i, int c, int, real gv) {
-      ob[(long long)i * g.nx + c] = A.sigma_l2 * gv;
-    });
+    band_adjoint<real, NT, RB, 0, 4>(g, T, pitch, i0, wx, wy, [&](int, int, real (&)[1]) {},
+                                     [&](int i, int c, int, real gv, const real (&)[1]) {
+                                       ob[(long long)i * g.nx + c] = A.sigma_l2 * gv;
+                                     });
   }
 }
 
@@ -153,23 +183,23 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, long long c_lo, long 
     real* zw = A.warm + chain * g.P;
     __syncthreads();
     if (A.warm_on) {
-      band_stage(X, pitch, zw, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS, real(1));
+      band_stage(X, pitch, zw, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     } else {
       for (int r = 0; r < Band<real, NT, RB>::XROWS; ++r)
         for (int c = threadIdx.x; c < g.nx; c += BAND_BT) X[r * pitch + BAND_PAD + c] = real(0);
+      __syncthreads();
     }
-    __syncthreads();
     band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
     const real* y0 = A.y + chain * 2 * g.P;
     const real* y1 = y0 + g.P;
     const real* ob = A.optb + (A.b_stride ? chain : 0) * g.P;
     double accb = 0, accu = 0;
-    band_adjoint<real, NT, RB>(g, T, pitch, i0, wx, wy, [&](int i, int c, int k, real gv) {
+    // operands of the pointwise part: [0] arg = x - tau (G^T y + z)  (or the prox argument), [1] sigma H^T b
+    auto pre = [&](int i, int c, real (&v)[2]) {
       const long long o = (long long)i * g.nx + c;
-      real arg;
       if (A.mode == 1) {
-        arg = A.in[chain * g.P + o];
+        v[0] = A.in[chain * g.P + o];
       } else {
         // G^T y in the accumulation order of pylops (axis 0 then axis 1); v[last] is never read
         real t = real(0);
@@ -178,9 +208,14 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, long long c_lo, long 
         if (c < g.nx - 1) t -= y1[o];
         if (c >= 1) t += y1[o - 1];
         if (A.zlin != nullptr) t += A.zlin[o];
-        arg = A.x[chain * g.P + o] - A.tau * t;   // algs.py:439/446: x - tau * ATy
+        v[0] = A.x[chain * g.P + o] - A.tau * t;   // algs.py:439/446: x - tau * ATy
       }
-      const real rhs = arg + A.tau * ob[o];       // pyproximal L2.prox: y = x + tau * OpTb
+      v[1] = ob[o];
+    };
+    band_adjoint<real, NT, RB, 2, 4>(g, T, pitch, i0, wx, wy, pre, [&](int i, int c, int k, real gv,
+                                                                        const real (&v)[2]) {
+      const long long o = (long long)i * g.nx + c;
+      const real rhs = v[0] + A.tau * v[1];       // pyproximal L2.prox: y = x + tau * OpTb
       const real zc = X[(k + E) * pitch + BAND_PAD + c];
       const real u = rhs - (zc + A.cA * gv);      // u = b - A x0
       A.u[chain * g.P + o] = u;
@@ -208,14 +243,14 @@ __device__ void band_v0(const UlpdaArgs<real>& A, long long c_lo, long long c_hi
     if (!A.st[chain].active) continue;
     const real su = (real)A.st[chain].su;
     __syncthreads();
-    band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS, su);
-    __syncthreads();
+    band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
     double acc = 0;
-    band_adjoint<real, NT, RB>(g, T, pitch, i0, wx, wy, [&](int i, int c, int k, real gv) {
+    band_adjoint<real, NT, RB, 0, 4>(g, T, pitch, i0, wx, wy, [&](int, int, real (&)[1]) {},
+                                     [&](int i, int c, int k, real gv, const real (&)[1]) {
       const long long o = chain * g.P + (long long)i * g.nx + c;
-      const real vv = X[(k + E) * pitch + BAND_PAD + c] + A.cA * gv;
+      const real vv = su * X[(k + E) * pitch + BAND_PAD + c] + A.cA * (su * gv);   // Op1 (su u): the scale commutes
       A.v[o] = vv;
       A.w[o] = vv;
       acc += (double)vv * (double)vv;
@@ -238,22 +273,30 @@ __device__ void band_ka(const UlpdaArgs<real>& A, long long c_lo, long long c_hi
     const real sv = (real)s.sv, sw = (real)s.sw, su = (real)s.su, t1 = (real)s.t1, t2 = (real)s.t2,
                alfa = (real)s.alfa;
     __syncthreads();
-    band_stage(X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS, sv);
-    __syncthreads();
+    band_stage(X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
     double accu = 0, accw = 0;
-    band_adjoint<real, NT, RB>(g, T, pitch, i0, wx, wy, [&](int i, int c, int k, real gv) {
+    auto pre = [&](int i, int c, real (&v)[3]) {
       const long long o = chain * g.P + (long long)i * g.nx + c;
-      const real vs = X[(k + E) * pitch + BAND_PAD + c];
+      v[0] = A.u[o];
+      if (s.pending) {
+        v[1] = A.w[o];
+        v[2] = A.warm[o];
+      }
+    };
+    band_adjoint<real, NT, RB, 3, 4>(g, T, pitch, i0, wx, wy, pre, [&](int i, int c, int k, real gv,
+                                                                        const real (&v)[3]) {
+      const long long o = chain * g.P + (long long)i * g.nx + c;
+      const real vs = sv * X[(k + E) * pitch + BAND_PAD + c];   // the stored v carries the pending scale sv
       if (s.pending) {   // deferred update of the previous LSQR iteration
-        real wv = sw * A.w[o];
-        A.warm[o] += t1 * wv;          // x = x + t1 * w
+        real wv = sw * v[1];
+        A.warm[o] = v[2] + t1 * wv;    // x = x + t1 * w
         wv = vs + t2 * wv;             // w = v + t2 * w
         A.w[o] = wv;
         accw += (double)wv * (double)wv;
       }
-      const real un = (vs + A.cA * gv) - alfa * (su * A.u[o]);   // u = A v - alfa u
+      const real un = (vs + A.cA * (sv * gv)) - alfa * (su * v[0]);   // u = A v - alfa u
       A.u[o] = un;
       accu += (double)un * (double)un;
     });
@@ -278,14 +321,15 @@ __device__ void band_kb(const UlpdaArgs<real>& A, long long c_lo, long long c_hi
     if (!s.active || !(s.beta > 0)) continue;
     const real su = (real)s.su, sv = (real)s.sv, beta = (real)s.beta;
     __syncthreads();
-    band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS, su);
-    __syncthreads();
+    band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
     double acc = 0;
-    band_adjoint<real, NT, RB>(g, T, pitch, i0, wx, wy, [&](int i, int c, int k, real gv) {
+    band_adjoint<real, NT, RB, 1, 4>(g, T, pitch, i0, wx, wy,
+                                     [&](int i, int c, real (&v)[1]) { v[0] = A.v[chain * g.P + (long long)i * g.nx + c]; },
+                                     [&](int i, int c, int k, real gv, const real (&v)[1]) {
       const long long o = chain * g.P + (long long)i * g.nx + c;
-      const real vn = (X[(k + E) * pitch + BAND_PAD + c] + A.cA * gv) - beta * (sv * A.v[o]);
+      const real vn = (su * X[(k + E) * pitch + BAND_PAD + c] + A.cA * (su * gv)) - beta * (sv * v[0]);
       A.v[o] = vn;
       acc += (double)vn * (double)vn;
     });
@@ -391,7 +435,7 @@ __device__ void band_dual(const UlpdaArgs<real>& A, long long c_lo, long long c_
 }
 
 template <typename real, int NT, int RB>
-__global__ void __launch_bounds__(BAND_BT) img_ulpda_band_kernel(const __grid_constant__ UlpdaArgs<real> A) {
+__global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid_constant__ UlpdaArgs<real> A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
   __shared__ double red[BAND_BT / 32];
