@@ -192,8 +192,8 @@ int lmc_img_ulpda_run(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr,
 
 /* ULPDA, row-band formulation (csrc/img_ulpda_band.inl): full-width bands of 16 rows staged in shared
  * memory, fused two-pass H^T H with compile-time taps, chains advanced in groups of `group` chains
- * (0 = as many as keep the LSQR vectors L2 resident), each group running all N iterations before
- * the next.  Same arguments, workspace, noise stream and results (same arithmetic per pixel) as
+ * (0 = all chains in lockstep; a smaller group keeps the LSQR vectors L2 resident), each group
+ * running all N iterations before the next.  Same arguments, workspace, noise stream and results (same arithmetic per pixel) as
  * lmc_img_ulpda_run; requires 5/6/7 blur taps on both axes (lmc_img_ulpda_band_supported() != 0). */
 int lmc_img_ulpda_band_supported(const lmc_img_problem* pb, int dtype);
 int lmc_img_ulpda_run_band(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, int dtype, int64_t C,

@@ -20,7 +20,7 @@ def sources():
 
 def build(force=False, verbose=False):
     srcs = sources()
-    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")] + [
+    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".inl"))] + [
         os.path.join(os.path.dirname(HERE), "include", "lmc_b200.h")]
     if (not force and os.path.isfile(OUT)
             and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in deps)):

@@ -54,12 +54,9 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
     A.g.tiles_y = (pb->ny + BAND_RB - 1) / BAND_RB;
     A.g.tiles = A.g.tiles_y;
     A.pitch = band_pitch(pb->nx);
-    if (group <= 0) {
-      // LSQR vectors u, v, w, z of a group stay L2 resident (about 3/4 of the 126 MB L2)
-      const double per_chain = 4.0 * (double)A.g.P * sizeof(real);
-      group = (long long)(96.0 * 1024 * 1024 / per_chain);
-      if (group < 1) group = 1;
-    }
+    // group <= 0: all chains in lockstep.  Measured on B200 (512x512, 256 chains): L2-sized groups of 16-48
+    // chains lose more to the extra grid barriers and to partial waves than they gain from L2 hits.
+    if (group <= 0) group = C;
     A.group = group < C ? group : C;
   }
   const size_t need = ulpda_ws_bytes<real>(pb->ny, pb->nx, C);
