@@ -22,10 +22,22 @@ bool band_supported(const lmc_img_problem* pb) {
   return smem <= 200 * 1024;
 }
 
-template <typename real, int NT>
+// two columns per thread: the tap windows of both passes must start on even columns and every array the
+// band phases touch with vector accesses must be aligned to two elements
+template <typename real>
+bool band_pairs(const UlpdaArgs<real>& A) {
+  if (A.g.ntap_x != 5 || A.g.lo_x != -2 || (A.g.nx & 1)) return false;
+  if (getenv("LMC_BAND_SCALAR") != nullptr) return false;   // experiments: one column per thread
+  const void* ptrs[] = {A.x, A.y, A.warm, A.optb, A.u, A.v, A.w, A.in, A.b};
+  for (const void* p : ptrs)
+    if (reinterpret_cast<size_t>(p) % (2 * sizeof(real)) != 0) return false;
+  return true;
+}
+
+template <typename real, int NT, int W>
 int launch_band(UlpdaArgs<real>& A, cudaStream_t st) {
   const size_t smem = Band<real, NT, BAND_RB>::smem_bytes(A.pitch);
-  auto kern = img_ulpda_band_kernel<real, NT, BAND_RB>;
+  auto kern = img_ulpda_band_kernel<real, NT, BAND_RB, W>;
   int dev = 0, sms = 0, occ = 0;
   LMC_CUDA_OK(cudaGetDevice(&dev));
   LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -35,6 +47,7 @@ int launch_band(UlpdaArgs<real>& A, cudaStream_t st) {
   const long long cap = (long long)sms * occ;
   const long long g = A.group < A.C ? A.group : A.C;
   const long long items = g * A.g.tiles;
+  LMC_REQUIRE(items < (1ll << 31) && A.g.P < (1ll << 31), "ULPDA band kernel: 32-bit item / pixel indices exceeded");
   int grid = (int)(items < cap ? items : cap);
   if (grid < 1) grid = 1;
   void* kargs[] = {(void*)&A};
@@ -118,9 +131,9 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
   if (band) {
     switch (pb->ntap_y) {
-      case 5: return launch_band<real, 5>(A, st);
-      case 6: return launch_band<real, 6>(A, st);
-      default: return launch_band<real, 7>(A, st);
+      case 5: return band_pairs(A) ? launch_band<real, 5, 2>(A, st) : launch_band<real, 5, 1>(A, st);
+      case 6: return launch_band<real, 6, 1>(A, st);
+      default: return launch_band<real, 7, 1>(A, st);
     }
   }
   return launch_persistent(img_ulpda_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);

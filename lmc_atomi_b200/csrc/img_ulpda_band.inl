@@ -5,14 +5,17 @@
 // is staged once in shared memory (coalesced rows, zero pad columns = the zero boundary of
 // Convolve2D); Op1 = I + tau sigma H^T H is then two fused separable passes with compile-time
 // tap counts, each a horizontal filter out of shared memory feeding a vertical sliding window in
-// registers (thread = image column), and the pointwise LSQR update of the phase runs in the
-// epilogue of the second pass.  Chains are advanced in groups whose LSQR vectors (u, v, w, z)
-// fit in the 126 MB L2, each group running all N sampler iterations before the next starts, so
-// the inner LSQR loop is served from L2 instead of HBM.
+// registers, and the pointwise LSQR update of the phase runs in the epilogue of the second pass.
+// A thread owns W adjacent image columns (W = 2 when the tap windows start on even columns: all
+// shared/global accesses become 8/16-byte vectors and the index arithmetic is paid once per pair).
+// The global operands of the epilogue are requested BEFORE the band is staged, so their latency is
+// covered by the staging and the forward pass.
+// Chains are advanced in groups (default: all), each group running all N sampler iterations.
 namespace {
 
 constexpr int BAND_PAD = 8;     // zero columns each side of a staged row (>= max taps - 1)
 constexpr int BAND_BT = 256;    // threads per CTA
+constexpr int BAND_NW = BAND_BT / 32;
 
 template <typename real, int NT, int RB>
 struct Band {
@@ -24,18 +27,40 @@ struct Band {
 
 __host__ __device__ inline int band_pitch(int nx) { return ((nx + 2 * BAND_PAD + 3) / 4) * 4; }
 
-__device__ __forceinline__ double band_block_sum(double v, double* red) {
-  v = lmc_warp_sum(v);
+// W adjacent elements moved as one vector
+template <typename real, int W>
+struct alignas(sizeof(real) * W) Pack {
+  real a[W];
+};
+template <typename real, int W>
+__device__ __forceinline__ Pack<real, W> ldp(const real* p) {
+  return *reinterpret_cast<const Pack<real, W>*>(p);
+}
+template <typename real, int W>
+__device__ __forceinline__ void stp(real* p, const Pack<real, W>& v) {
+  *reinterpret_cast<Pack<real, W>*>(p) = v;
+}
+
+// block-wide fp64 sums of two values behind ONE barrier (fixed order: deterministic); results valid in
+// thread 0.  `red` (2 x BAND_NW doubles) is next written only after the barrier at the top of the next item.
+__device__ __forceinline__ void band_block_sum2(double& a, double& b, double* red) {
+  a = lmc_warp_sum(a);
+  b = lmc_warp_sum(b);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) red[wid] = v;
-  __syncthreads();
-  double s = 0;
-  if (threadIdx.x == 0) {
-#pragma unroll
-    for (int i = 0; i < BAND_BT / 32; ++i) s += red[i];
+  if (lane == 0) {
+    red[wid] = a;
+    red[BAND_NW + wid] = b;
   }
-  return s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    a = 0;
+    b = 0;
+#pragma unroll
+    for (int i = 0; i < BAND_NW; ++i) {
+      a += red[i];
+      b += red[BAND_NW + i];
+    }
+  }
 }
 
 // rows [ifirst, ifirst + rows) of src -> S (zero outside the image), as 16-byte cp.async copies when the
@@ -45,21 +70,39 @@ __device__ __forceinline__ void band_stage(real* S, int pitch, const real* __res
                                            int rows) {
   constexpr int EPV = 16 / sizeof(real);
   const bool vec = (nx % EPV == 0) && ((reinterpret_cast<size_t>(src) & 15) == 0);
-  for (int r = 0; r < rows; ++r) {
-    const int i = ifirst + r;
-    real* dst = S + r * pitch + BAND_PAD;
-    if (i >= 0 && i < ny) {
-      const real* s = src + (long long)i * nx;
-      if (vec) {
-        for (int c = threadIdx.x * EPV; c < nx; c += BAND_BT * EPV) {
-          const unsigned d = (unsigned)__cvta_generic_to_shared(dst + c);
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(s + c) : "memory");
+  const int cpr = nx / EPV;   // 16-byte chunks per row
+  if (vec && cpr <= BAND_BT && BAND_BT % cpr == 0) {
+    // a thread keeps its chunk column and walks down the rows: no per-copy index arithmetic
+    const int rstep = BAND_BT / cpr, r0 = threadIdx.x / cpr, c = (threadIdx.x - r0 * cpr) * EPV;
+    real* dst = S + r0 * pitch + BAND_PAD + c;
+    const real* s = src + (long long)(ifirst + r0) * nx + c;
+    const int dstep = rstep * pitch, sstep = rstep * nx;
+    for (int r = r0; r < rows; r += rstep, dst += dstep, s += sstep) {
+      const int i = ifirst + r;
+      if (i >= 0 && i < ny) {
+        const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(s) : "memory");
+      } else {
+        *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+  } else {
+    for (int r = 0; r < rows; ++r) {
+      const int i = ifirst + r;
+      real* dst = S + r * pitch + BAND_PAD;
+      if (i >= 0 && i < ny) {
+        const real* s = src + (long long)i * nx;
+        if (vec) {
+          for (int c = threadIdx.x * EPV; c < nx; c += BAND_BT * EPV) {
+            const unsigned d = (unsigned)__cvta_generic_to_shared(dst + c);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(s + c) : "memory");
+          }
+        } else {
+          for (int c = threadIdx.x; c < nx; c += BAND_BT) dst[c] = s[c];
         }
       } else {
-        for (int c = threadIdx.x; c < nx; c += BAND_BT) dst[c] = s[c];
+        for (int c = threadIdx.x; c < nx; c += BAND_BT) dst[c] = real(0);
       }
-    } else {
-      for (int c = threadIdx.x; c < nx; c += BAND_BT) dst[c] = real(0);
     }
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
@@ -67,43 +110,81 @@ __device__ __forceinline__ void band_stage(real* S, int pitch, const real* __res
   __syncthreads();
 }
 
+// the NT + W - 1 consecutive elements starting at p (p is W-element aligned)
+template <typename real, int NT, int W>
+__device__ __forceinline__ void band_taps(const real* p, real (&e)[NT + W - 1]) {
+  if constexpr (W == 1) {
+#pragma unroll
+    for (int s = 0; s < NT; ++s) e[s] = p[s];
+  } else {
+    constexpr int NE = NT + W - 1, NV = (NE + W - 1) / W;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const Pack<real, W> t = ldp<real, W>(p + W * v);
+#pragma unroll
+      for (int q = 0; q < W; ++q)
+        if (W * v + q < NE) e[W * v + q] = t.a[q];
+    }
+  }
+}
+
+template <typename real, int W, int NPRE, int PFD>
+using BandPf = Pack<real, W>[2][PFD][NPRE > 0 ? NPRE : 1];   // two blocks of PFD rows in flight
+
+// request the epilogue operands of the first two row blocks of columns [c, c + W)
+template <typename real, int RB, int W, int NPRE, int PFD, class Pre>
+__device__ __forceinline__ void band_prefetch(const Geom<real>& g, int i0, int c, BandPf<real, W, NPRE, PFD>& pf,
+                                              Pre&& pre) {
+  constexpr int NBLK = RB / PFD;
+  if (NPRE > 0 && c < g.nx) {
+#pragma unroll
+    for (int bl = 0; bl < 2 && bl < NBLK; ++bl)
+#pragma unroll
+      for (int kk = 0; kk < PFD; ++kk) pre(min(i0 + bl * PFD + kk, g.ny - 1), c, pf[bl][kk]);
+  }
+}
+
 // second half of the operator: T (rows i0 - hi_y .. of a row-masked image) -> H^T T on the band.
-// pre(i, c, v) loads the NPRE global operands of pixel (i, c) of the phase's pointwise update; they are
-// fetched PFD rows ahead (all loads of a block in flight together), epi(i, c, k, value, v) consumes them
-// (k = row within the band).  Both only for in-image pixels.
-template <typename real, int NT, int RB, int NPRE, int PFD, class Pre, class Epi>
-__device__ __forceinline__ void band_adjoint(const Geom<real>& g, const real* T, int pitch, int i0, const real (&wx)[NT],
-                                             const real (&wy)[NT], Pre&& pre, Epi&& epi) {
+// pre(i, c, v) loads the NPRE global operands of pixels (i, c .. c+W-1) of the phase's pointwise update; they
+// are fetched PFD rows ahead (rows past the image are clamped, not skipped: no branch around the loads);
+// the first two blocks of the thread's first column group arrive in `pf` (band_prefetch, issued by the
+// caller before staging).  epi(i, c, k, value, v) consumes them (k = row within the band), in-image rows only.
+template <typename real, int NT, int RB, int W, int NPRE, int PFD, class Pre, class Epi>
+__device__ __forceinline__ void band_adjoint(const Geom<real>& g, const real* T, int pitch, int i0, const real* wx,
+                                             const real* wy, BandPf<real, W, NPRE, PFD>& pf, Pre&& pre,
+                                             Epi&& epi) {
   static_assert(RB % PFD == 0, "prefetch depth must divide the band height");
   constexpr int NBLK = RB / PFD;
   const int lox = g.lo_x;
-  for (int c = threadIdx.x; c < g.nx; c += BAND_BT) {
-    const real* trow = T + BAND_PAD + c - lox;
-    real win[NT];
-    real pf[2][PFD][NPRE > 0 ? NPRE : 1];   // two blocks of PFD rows in flight
-    if (NPRE > 0) {
-#pragma unroll
-      for (int bl = 0; bl < 2 && bl < NBLK; ++bl)
-#pragma unroll
-        for (int kk = 0; kk < PFD; ++kk)
-          if (i0 + bl * PFD + kk < g.ny) pre(i0 + bl * PFD + kk, c, pf[bl][kk]);
-    }
+  for (int c = W * threadIdx.x; c < g.nx; c += W * BAND_BT) {
+    if (c != W * (int)threadIdx.x) band_prefetch<real, RB, W, NPRE, PFD>(g, i0, c, pf, pre);
+    const real* trow = T + BAND_PAD + c - lox - (NT - 1);
+    real win[W][NT];
 #pragma unroll
     for (int jj = 0; jj < RB + NT - 1; ++jj) {
-      real u = real(0);
+      real e[NT + W - 1];
+      band_taps<real, NT, W>(trow + jj * pitch, e);
 #pragma unroll
-      for (int s = 0; s < NT; ++s) u = Math<real>::fma(wx[s], trow[jj * pitch - s], u);
-      win[jj % NT] = u;
+      for (int q = 0; q < W; ++q) {
+        real u = real(0);
+#pragma unroll
+        for (int s = 0; s < NT; ++s) u = Math<real>::fma(wx[s], e[NT - 1 - s + q], u);
+        win[q][jj % NT] = u;
+      }
       if (jj >= NT - 1) {
         const int k = jj - (NT - 1), i = i0 + k;
-        real gv = real(0);
+        Pack<real, W> gv;
 #pragma unroll
-        for (int t = 0; t < NT; ++t) gv = Math<real>::fma(wy[t], win[(k + NT - 1 - t) % NT], gv);
+        for (int q = 0; q < W; ++q) {
+          real r = real(0);
+#pragma unroll
+          for (int t = 0; t < NT; ++t) r = Math<real>::fma(wy[t], win[q][(k + NT - 1 - t) % NT], r);
+          gv.a[q] = r;
+        }
         if (i < g.ny) epi(i, c, k, gv, pf[(k / PFD) & 1][k % PFD]);
         if (NPRE > 0 && (k % PFD) == PFD - 1 && k / PFD + 2 < NBLK) {   // block consumed: fetch block + 2 into its slot
 #pragma unroll
-          for (int kk = 0; kk < PFD; ++kk)
-            if (i0 + k + 1 + PFD + kk < g.ny) pre(i0 + k + 1 + PFD + kk, c, pf[(k / PFD) & 1][kk]);
+          for (int kk = 0; kk < PFD; ++kk) pre(min(i0 + k + 1 + PFD + kk, g.ny - 1), c, pf[(k / PFD) & 1][kk]);
         }
       }
     }
@@ -111,38 +192,50 @@ __device__ __forceinline__ void band_adjoint(const Geom<real>& g, const real* T,
 }
 
 // first half: staged X (rows i0 - E ..) -> T = mask_rows(H X) on rows [i0 - hi_y, i0 + RB - lo_y)
-template <typename real, int NT, int RB>
+template <typename real, int NT, int RB, int W>
 __device__ __forceinline__ void band_forward(const Geom<real>& g, const real* X, real* T, int pitch, int i0,
-                                             const real (&wx)[NT], const real (&wy)[NT]) {
+                                             const real* wx, const real* wy) {
   const int lox = g.lo_x, hi_y = g.lo_y + NT - 1;
-  for (int c = threadIdx.x; c < g.nx; c += BAND_BT) {
+  for (int c = W * threadIdx.x; c < g.nx; c += W * BAND_BT) {
     const real* xrow = X + BAND_PAD + c + lox;
-    real win[NT];
+    real* trow = T + BAND_PAD + c;
+    real win[W][NT];
 #pragma unroll
     for (int jj = 0; jj < RB + 2 * (NT - 1); ++jj) {
-      real t1 = real(0);
+      real e[NT + W - 1];
+      band_taps<real, NT, W>(xrow + jj * pitch, e);
 #pragma unroll
-      for (int s = 0; s < NT; ++s) t1 = Math<real>::fma(wx[s], xrow[jj * pitch + s], t1);
-      win[jj % NT] = t1;
+      for (int q = 0; q < W; ++q) {
+        real t1 = real(0);
+#pragma unroll
+        for (int s = 0; s < NT; ++s) t1 = Math<real>::fma(wx[s], e[s + q], t1);
+        win[q][jj % NT] = t1;
+      }
       if (jj >= NT - 1) {
         const int o = jj - (NT - 1), i = i0 - hi_y + o;
-        real res = real(0);
+        Pack<real, W> res;
+#pragma unroll
+        for (int q = 0; q < W; ++q) res.a[q] = real(0);
         if (i >= 0 && i < g.ny) {
 #pragma unroll
-          for (int t = 0; t < NT; ++t) res = Math<real>::fma(wy[t], win[(o + t) % NT], res);
+          for (int q = 0; q < W; ++q) {
+            real r = real(0);
+#pragma unroll
+            for (int t = 0; t < NT; ++t) r = Math<real>::fma(wy[t], win[q][(o + t) % NT], r);
+            res.a[q] = r;
+          }
         }
-        T[o * pitch + BAND_PAD + c] = res;
+        stp<real, W>(trow + o * pitch, res);
       }
     }
   }
 }
 
 template <typename real>
-__device__ __forceinline__ void band_of(const Geom<real>& g, long long w, long long c_lo, int RB, long long& chain,
-                                        int& i0) {
-  const long long cl = w / g.tiles;
+__device__ __forceinline__ void band_of(const Geom<real>& g, int w, long long c_lo, int RB, long long& chain, int& i0) {
+  const int cl = w / g.tiles;
   chain = c_lo + cl;
-  i0 = (int)(w - cl * g.tiles) * RB;
+  i0 = (w - cl * g.tiles) * RB;
 }
 
 #define BAND_ITEMS_LOOP                                                        \
@@ -150,13 +243,14 @@ __device__ __forceinline__ void band_of(const Geom<real>& g, long long w, long l
   real* X = smem;                                                              \
   real* T = smem + Band<real, NT, RB>::XROWS * A.pitch;                        \
   const int pitch = A.pitch;                                                   \
-  const long long items = (c_hi - c_lo) * g.tiles, pall = A.C * g.tiles;       \
+  const int items = (int)(c_hi - c_lo) * g.tiles;                              \
+  const long long pall = A.C * g.tiles;                                        \
   (void)X; (void)T; (void)pall;                                                \
-  for (long long w = blockIdx.x; w < items; w += gridDim.x)
+  for (int w = blockIdx.x; w < items; w += gridDim.x)
 
 // ---------------------------------------------------------------- P0: optb = sigma H^T b
-template <typename real, int NT, int RB>
-__device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real (&wx)[NT], const real (&wy)[NT]) {
+template <typename real, int NT, int RB, int W>
+__device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real* wx, const real* wy) {
   const long long c_lo = 0, c_hi = A.b_stride ? A.C : 1;
   const int hi_y = A.g.lo_y + NT - 1;
   BAND_ITEMS_LOOP {
@@ -165,22 +259,58 @@ __device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real (&wx)
     __syncthreads();
     band_stage(T, pitch, A.b + chain * A.b_stride, g.ny, g.nx, i0 - hi_y, Band<real, NT, RB>::TROWS);
     real* ob = A.optb + chain * g.P;
-    band_adjoint<real, NT, RB, 0, 4>(g, T, pitch, i0, wx, wy, [&](int, int, real (&)[1]) {},
-                                     [&](int i, int c, int, real gv, const real (&)[1]) {
-                                       ob[(long long)i * g.nx + c] = A.sigma_l2 * gv;
-                                     });
+    BandPf<real, W, 0, 4> pf;
+    band_adjoint<real, NT, RB, W, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, Pack<real, W> (&)[1]) {},
+                                        [&](int i, int c, int, const Pack<real, W>& gv, const Pack<real, W> (&)[1]) {
+                                          Pack<real, W> o;
+#pragma unroll
+                                          for (int q = 0; q < W; ++q) o.a[q] = A.sigma_l2 * gv.a[q];
+                                          stp<real, W>(ob + i * g.nx + c, o);
+                                        });
   }
 }
 
 // ---------------------------------------------------------------- P1: rhs, u = rhs - Op1 warm
-template <typename real, int NT, int RB>
+template <typename real, int NT, int RB, int W>
 __device__ void band_primal_init(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
-                                 const real (&wx)[NT], const real (&wy)[NT]) {
+                                 const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     real* zw = A.warm + chain * g.P;
+    real* uC = A.u + chain * g.P;
+    const real* y0 = A.y + chain * 2 * g.P;
+    const real* y1 = y0 + g.P;
+    const real* xC = A.x + chain * g.P;
+    const real* inC = A.in + chain * g.P;
+    const real* ob = A.optb + (A.b_stride ? chain : 0) * g.P;
+    // operands of the pointwise part: [0] arg = x - tau (G^T y + z)  (or the prox argument), [1] sigma H^T b
+    auto pre = [&](int i, int c, Pack<real, W> (&v)[2]) {
+      const int o = i * g.nx + c;
+      if (A.mode == 1) {
+        v[0] = ldp<real, W>(inC + o);
+      } else {
+        // G^T y in the accumulation order of pylops (axis 0 then axis 1); v[last] is never read
+        const Pack<real, W> xc = ldp<real, W>(xC + o), y0c = ldp<real, W>(y0 + o), y1c = ldp<real, W>(y1 + o);
+        Pack<real, W> y0u = y0c;
+        if (i >= 1) y0u = ldp<real, W>(y0 + o - g.nx);
+        const real y1l = (c >= 1) ? y1[o - 1] : real(0);
+#pragma unroll
+        for (int q = 0; q < W; ++q) {
+          real t = real(0);
+          if (i < g.ny - 1) t -= y0c.a[q];
+          if (i >= 1) t += y0u.a[q];
+          if (c + q < g.nx - 1) t -= y1c.a[q];
+          if (c + q >= 1) t += (q == 0) ? y1l : y1c.a[q > 0 ? q - 1 : 0];
+          if (A.zlin != nullptr) t += A.zlin[o + q];
+          v[0].a[q] = xc.a[q] - A.tau * t;   // algs.py:439/446: x - tau * ATy
+        }
+      }
+      v[1] = ldp<real, W>(ob + o);
+    };
+    BandPf<real, W, 2, 4> pf;
+    band_prefetch<real, RB, W, 2, 4>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
     if (A.warm_on) {
       band_stage(X, pitch, zw, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
@@ -189,152 +319,173 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, long long c_lo, long 
         for (int c = threadIdx.x; c < g.nx; c += BAND_BT) X[r * pitch + BAND_PAD + c] = real(0);
       __syncthreads();
     }
-    band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
+    band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
-    const real* y0 = A.y + chain * 2 * g.P;
-    const real* y1 = y0 + g.P;
-    const real* ob = A.optb + (A.b_stride ? chain : 0) * g.P;
     double accb = 0, accu = 0;
-    // operands of the pointwise part: [0] arg = x - tau (G^T y + z)  (or the prox argument), [1] sigma H^T b
-    auto pre = [&](int i, int c, real (&v)[2]) {
-      const long long o = (long long)i * g.nx + c;
-      if (A.mode == 1) {
-        v[0] = A.in[chain * g.P + o];
-      } else {
-        // G^T y in the accumulation order of pylops (axis 0 then axis 1); v[last] is never read
-        real t = real(0);
-        if (i < g.ny - 1) t -= y0[o];
-        if (i >= 1) t += y0[o - g.nx];
-        if (c < g.nx - 1) t -= y1[o];
-        if (c >= 1) t += y1[o - 1];
-        if (A.zlin != nullptr) t += A.zlin[o];
-        v[0] = A.x[chain * g.P + o] - A.tau * t;   // algs.py:439/446: x - tau * ATy
+    band_adjoint<real, NT, RB, W, 2, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
+                                                                              const Pack<real, W> (&v)[2]) {
+      const int o = i * g.nx + c;
+      const Pack<real, W> zc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
+      Pack<real, W> un;
+#pragma unroll
+      for (int q = 0; q < W; ++q) {
+        const real rhs = v[0].a[q] + A.tau * v[1].a[q];       // pyproximal L2.prox: y = x + tau * OpTb
+        const real u = rhs - (zc.a[q] + A.cA * gv.a[q]);      // u = b - A x0
+        un.a[q] = u;
+        accb += (double)rhs * (double)rhs;
+        accu += (double)u * (double)u;
       }
-      v[1] = ob[o];
-    };
-    band_adjoint<real, NT, RB, 2, 4>(g, T, pitch, i0, wx, wy, pre, [&](int i, int c, int k, real gv,
-                                                                        const real (&v)[2]) {
-      const long long o = (long long)i * g.nx + c;
-      const real rhs = v[0] + A.tau * v[1];       // pyproximal L2.prox: y = x + tau * OpTb
-      const real zc = X[(k + E) * pitch + BAND_PAD + c];
-      const real u = rhs - (zc + A.cA * gv);      // u = b - A x0
-      A.u[chain * g.P + o] = u;
-      if (!A.warm_on) zw[o] = real(0);
-      accb += (double)rhs * (double)rhs;
-      accu += (double)u * (double)u;
+      stp<real, W>(uC + o, un);
+      if (!A.warm_on) {
+#pragma unroll
+        for (int q = 0; q < W; ++q) un.a[q] = real(0);
+        stp<real, W>(zw + o, un);
+      }
     });
-    const double sb = band_block_sum(accb, red);
-    const double su = band_block_sum(accu, red);
+    band_block_sum2(accb, accu, red);
     if (threadIdx.x == 0) {
-      A.partial[chain * g.tiles + i0 / RB] = sb;
-      A.partial[pall + chain * g.tiles + i0 / RB] = su;
+      A.partial[chain * g.tiles + i0 / RB] = accb;
+      A.partial[pall + chain * g.tiles + i0 / RB] = accu;
     }
   }
 }
 
 // ---------------------------------------------------------------- P2: v = Op1 (su * u); w = v
-template <typename real, int NT, int RB>
+template <typename real, int NT, int RB, int W>
 __device__ void band_v0(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
-                        const real (&wx)[NT], const real (&wy)[NT]) {
+                        const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     if (!A.st[chain].active) continue;
     const real su = (real)A.st[chain].su;
+    real* vC = A.v + chain * g.P;
+    real* wC = A.w + chain * g.P;
     __syncthreads();
     band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
-    band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
+    band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
-    double acc = 0;
-    band_adjoint<real, NT, RB, 0, 4>(g, T, pitch, i0, wx, wy, [&](int, int, real (&)[1]) {},
-                                     [&](int i, int c, int k, real gv, const real (&)[1]) {
-      const long long o = chain * g.P + (long long)i * g.nx + c;
-      const real vv = su * X[(k + E) * pitch + BAND_PAD + c] + A.cA * (su * gv);   // Op1 (su u): the scale commutes
-      A.v[o] = vv;
-      A.w[o] = vv;
-      acc += (double)vv * (double)vv;
+    double acc = 0, none = 0;
+    BandPf<real, W, 0, 4> pf;
+    band_adjoint<real, NT, RB, W, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, Pack<real, W> (&)[1]) {},
+                                        [&](int i, int c, int k, const Pack<real, W>& gv, const Pack<real, W> (&)[1]) {
+      const int o = i * g.nx + c;
+      const Pack<real, W> xc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
+      Pack<real, W> vn;
+#pragma unroll
+      for (int q = 0; q < W; ++q) {
+        const real vv = su * xc.a[q] + A.cA * (su * gv.a[q]);   // Op1 (su u): the scale commutes
+        vn.a[q] = vv;
+        acc += (double)vv * (double)vv;
+      }
+      stp<real, W>(vC + o, vn);
+      stp<real, W>(wC + o, vn);
     });
-    const double s = band_block_sum(acc, red);
-    if (threadIdx.x == 0) A.partial[pall + chain * g.tiles + i0 / RB] = s;
+    band_block_sum2(acc, none, red);
+    if (threadIdx.x == 0) A.partial[pall + chain * g.tiles + i0 / RB] = acc;
   }
 }
 
 // ---------------------------------------------------------------- Ka: [deferred x, w update]; u = Op1 v - alfa u
-template <typename real, int NT, int RB>
+template <typename real, int NT, int RB, int W>
 __device__ void band_ka(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
-                        const real (&wx)[NT], const real (&wy)[NT]) {
+                        const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
-    const LsqrState s = A.st[chain];
-    if (!s.active) continue;
-    const real sv = (real)s.sv, sw = (real)s.sw, su = (real)s.su, t1 = (real)s.t1, t2 = (real)s.t2,
-               alfa = (real)s.alfa;
-    __syncthreads();
-    band_stage(X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
-    band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
-    __syncthreads();
-    double accu = 0, accw = 0;
-    auto pre = [&](int i, int c, real (&v)[3]) {
-      const long long o = chain * g.P + (long long)i * g.nx + c;
-      v[0] = A.u[o];
-      if (s.pending) {
-        v[1] = A.w[o];
-        v[2] = A.warm[o];
+    const LsqrState* sp = A.st + chain;
+    if (!sp->active) continue;
+    const bool pending = sp->pending != 0;
+    const real sv = (real)sp->sv, sw = (real)sp->sw, su = (real)sp->su, t1 = (real)sp->t1, t2 = (real)sp->t2,
+               alfa = (real)sp->alfa;
+    real* uC = A.u + chain * g.P;
+    real* wC = A.w + chain * g.P;
+    real* zC = A.warm + chain * g.P;
+    auto pre = [&](int i, int c, Pack<real, W> (&v)[3]) {
+      const int o = i * g.nx + c;
+      v[0] = ldp<real, W>(uC + o);
+      if (pending) {
+        v[1] = ldp<real, W>(wC + o);
+        v[2] = ldp<real, W>(zC + o);
       }
     };
-    band_adjoint<real, NT, RB, 3, 4>(g, T, pitch, i0, wx, wy, pre, [&](int i, int c, int k, real gv,
-                                                                        const real (&v)[3]) {
-      const long long o = chain * g.P + (long long)i * g.nx + c;
-      const real vs = sv * X[(k + E) * pitch + BAND_PAD + c];   // the stored v carries the pending scale sv
-      if (s.pending) {   // deferred update of the previous LSQR iteration
-        real wv = sw * v[1];
-        A.warm[o] = v[2] + t1 * wv;    // x = x + t1 * w
-        wv = vs + t2 * wv;             // w = v + t2 * w
-        A.w[o] = wv;
-        accw += (double)wv * (double)wv;
+    BandPf<real, W, 3, 4> pf;
+    band_prefetch<real, RB, W, 3, 4>(g, i0, W * threadIdx.x, pf, pre);
+    __syncthreads();
+    band_stage(X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
+    band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
+    __syncthreads();
+    double accu = 0, accw = 0;
+    band_adjoint<real, NT, RB, W, 3, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
+                                                                              const Pack<real, W> (&v)[3]) {
+      const int o = i * g.nx + c;
+      const Pack<real, W> xc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
+      Pack<real, W> un, wn, zn;
+#pragma unroll
+      for (int q = 0; q < W; ++q) {
+        const real vs = sv * xc.a[q];   // the stored v carries the pending scale sv
+        if (pending) {   // deferred update of the previous LSQR iteration
+          real wv = sw * v[1].a[q];
+          zn.a[q] = v[2].a[q] + t1 * wv;    // x = x + t1 * w
+          wv = vs + t2 * wv;                // w = v + t2 * w
+          wn.a[q] = wv;
+          accw += (double)wv * (double)wv;
+        }
+        const real u1 = (vs + A.cA * (sv * gv.a[q])) - alfa * (su * v[0].a[q]);   // u = A v - alfa u
+        un.a[q] = u1;
+        accu += (double)u1 * (double)u1;
       }
-      const real un = (vs + A.cA * (sv * gv)) - alfa * (su * v[0]);   // u = A v - alfa u
-      A.u[o] = un;
-      accu += (double)un * (double)un;
+      if (pending) {
+        stp<real, W>(zC + o, zn);
+        stp<real, W>(wC + o, wn);
+      }
+      stp<real, W>(uC + o, un);
     });
-    const double s1 = band_block_sum(accu, red);
-    const double s2 = band_block_sum(accw, red);
+    band_block_sum2(accu, accw, red);
     if (threadIdx.x == 0) {
-      A.partial[pall + chain * g.tiles + i0 / RB] = s1;
-      A.partial[2 * pall + chain * g.tiles + i0 / RB] = s2;
+      A.partial[pall + chain * g.tiles + i0 / RB] = accu;
+      A.partial[2 * pall + chain * g.tiles + i0 / RB] = accw;
     }
   }
 }
 
 // ---------------------------------------------------------------- Kb: v = Op1 u - beta v
-template <typename real, int NT, int RB>
+template <typename real, int NT, int RB, int W>
 __device__ void band_kb(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
-                        const real (&wx)[NT], const real (&wy)[NT]) {
+                        const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
-    const LsqrState s = A.st[chain];
-    if (!s.active || !(s.beta > 0)) continue;
-    const real su = (real)s.su, sv = (real)s.sv, beta = (real)s.beta;
+    const LsqrState* sp = A.st + chain;
+    if (!sp->active || !(sp->beta > 0)) continue;
+    const real su = (real)sp->su, sv = (real)sp->sv, beta = (real)sp->beta;
+    real* vC = A.v + chain * g.P;
+    auto pre = [&](int i, int c, Pack<real, W> (&v)[1]) { v[0] = ldp<real, W>(vC + i * g.nx + c); };
+    BandPf<real, W, 1, 4> pf;
+    band_prefetch<real, RB, W, 1, 4>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
     band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
-    band_forward<real, NT, RB>(g, X, T, pitch, i0, wx, wy);
+    band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
-    double acc = 0;
-    band_adjoint<real, NT, RB, 1, 4>(g, T, pitch, i0, wx, wy,
-                                     [&](int i, int c, real (&v)[1]) { v[0] = A.v[chain * g.P + (long long)i * g.nx + c]; },
-                                     [&](int i, int c, int k, real gv, const real (&v)[1]) {
-      const long long o = chain * g.P + (long long)i * g.nx + c;
-      const real vn = (su * X[(k + E) * pitch + BAND_PAD + c] + A.cA * (su * gv)) - beta * (sv * v[0]);
-      A.v[o] = vn;
-      acc += (double)vn * (double)vn;
+    double acc = 0, none = 0;
+    band_adjoint<real, NT, RB, W, 1, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
+                                                                              const Pack<real, W> (&v)[1]) {
+      const int o = i * g.nx + c;
+      const Pack<real, W> xc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
+      Pack<real, W> vn;
+#pragma unroll
+      for (int q = 0; q < W; ++q) {
+        const real v1 = (su * xc.a[q] + A.cA * (su * gv.a[q])) - beta * (sv * v[0].a[q]);
+        vn.a[q] = v1;
+        acc += (double)v1 * (double)v1;
+      }
+      stp<real, W>(vC + o, vn);
     });
-    const double s1 = band_block_sum(acc, red);
-    if (threadIdx.x == 0) A.partial[pall + chain * g.tiles + i0 / RB] = s1;
+    band_block_sum2(acc, none, red);
+    if (threadIdx.x == 0) A.partial[pall + chain * g.tiles + i0 / RB] = acc;
   }
 }
 
@@ -342,14 +493,14 @@ __device__ void band_kb(const UlpdaArgs<real>& A, long long c_lo, long long c_hi
 template <typename real, int RB>
 __device__ void band_primal_final(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, long long n) {
   const Geom<real>& g = A.g;
-  const long long items = (c_hi - c_lo) * g.tiles;
+  const int items = (int)(c_hi - c_lo) * g.tiles;
   const int quads_per_row = (g.nx + 3) / 4;
   const unsigned long long it_global = A.iter_offset + (unsigned long long)n;
   const bool stats = (A.mean != nullptr) && ((long long)it_global >= A.burnin);
   const real inv_cnt = real(1) / (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
   const real cntn = (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
   (void)inv_cnt;
-  for (long long w = blockIdx.x; w < items; w += gridDim.x) {
+  for (int w = blockIdx.x; w < items; w += gridDim.x) {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     const LsqrState s = A.st[chain];
@@ -394,8 +545,8 @@ __device__ void band_primal_final(const UlpdaArgs<real>& A, long long c_lo, long
 template <typename real, int RB>
 __device__ void band_dual(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, long long n) {
   const Geom<real>& g = A.g;
-  const long long items = (c_hi - c_lo) * g.tiles;
-  for (long long w = blockIdx.x; w < items; w += gridDim.x) {
+  const int items = (int)(c_hi - c_lo) * g.tiles;
+  for (int w = blockIdx.x; w < items; w += gridDim.x) {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     const real* xh = A.xhat + chain * g.P;
@@ -434,25 +585,22 @@ __device__ void band_dual(const UlpdaArgs<real>& A, long long c_lo, long long c_
   }
 }
 
-template <typename real, int NT, int RB>
+template <typename real, int NT, int RB, int W>
 __global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid_constant__ UlpdaArgs<real> A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
-  __shared__ double red[BAND_BT / 32];
+  __shared__ double red[2 * BAND_NW];
   cg::grid_group grid = cg::this_grid();
-  real wx[NT], wy[NT];
-#pragma unroll
-  for (int t = 0; t < NT; ++t) {
-    wx[t] = A.g.wx[t];
-    wy[t] = A.g.wy[t];
-  }
+  // the taps stay in the kernel-parameter constant bank: FFMA reads them as c[0][..] operands, no registers
+  const real* wx = A.g.wx;
+  const real* wy = A.g.wy;
   // pad columns (and everything else) zero once; the phases only ever write columns [0, nx)
   {
     const int n = (Band<real, NT, RB>::XROWS + Band<real, NT, RB>::TROWS) * A.pitch;
     for (int idx = threadIdx.x; idx < n; idx += BAND_BT) smem[idx] = real(0);
   }
   __syncthreads();
-  band_optb<real, NT, RB>(A, smem, wx, wy);
+  band_optb<real, NT, RB, W>(A, smem, wx, wy);
   grid.sync();
   for (long long c_lo = 0; c_lo < A.C; c_lo += A.group) {
     const long long c_hi = (c_lo + A.group < A.C) ? c_lo + A.group : A.C;
@@ -462,22 +610,22 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid
         grid.sync();
       }
       if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-      band_primal_init<real, NT, RB>(A, c_lo, c_hi, smem, red, wx, wy);
+      band_primal_init<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
       grid.sync();
       phase_s1(A, c_lo, c_hi);
       grid.sync();
-      band_v0<real, NT, RB>(A, c_lo, c_hi, smem, red, wx, wy);
+      band_v0<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
       grid.sync();
       phase_s2(A, c_lo, c_hi);
       grid.sync();
       while (*(volatile int*)A.n_active != 0) {
         grid.sync();   // everyone has read n_active before it is reset
         if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-        band_ka<real, NT, RB>(A, c_lo, c_hi, smem, red, wx, wy);
+        band_ka<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
         grid.sync();
         phase_sa(A, c_lo, c_hi);
         grid.sync();
-        band_kb<real, NT, RB>(A, c_lo, c_hi, smem, red, wx, wy);
+        band_kb<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
         grid.sync();
         phase_sb(A, c_lo, c_hi);
         grid.sync();
