@@ -77,6 +77,7 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
               io->workspace_bytes, need);
   char* ws = (char*)io->d_workspace;
   A.n_active = (int*)ws;
+  A.queue = (int*)(ws + 128);
   unsigned long long* local_counters = (unsigned long long*)(ws + 64);
   ws += 256;
   A.st = (LsqrState*)ws;

@@ -66,6 +66,7 @@ struct UlpdaArgs {
   int mode;  // 0 = ULPDA, 1 = L2 prox only
   // band kernel only (img_ulpda_band.inl)
   int pitch;        // shared-memory row pitch in elements
+  int* queue;       // 4 work-queue counters (BandSched)
   long long group;  // chains advanced together (working set kept near the L2 size)
 };
 

@@ -238,6 +238,31 @@ __device__ __forceinline__ void band_of(const Geom<real>& g, int w, long long c_
   i0 = (w - cl * g.tiles) * RB;
 }
 
+// Dynamic work distribution: the CTAs of a phase draw items from a global counter instead of striding, so
+// a CTA on a slower path to memory (far L2 partition, busier SM) simply takes fewer items and the grid
+// barrier at the end of the phase is reached together.  Thread 0 draws the next item at the START of the
+// current one (the atomic's latency is covered by the item) and publishes it through shared memory at the
+// barrier that opens the next round.  Results do not depend on which CTA ran an item (one partial per item).
+struct BandSched {
+  int* q;        // 4 rotating global counters: phase p uses q[p & 3] and re-arms q[(p + 2) & 3]
+  int* s_next;   // 2 shared ints (double-buffered by round)
+  int phase, round, nxt;
+  __device__ __forceinline__ void begin() {
+    if (blockIdx.x == 0 && threadIdx.x == 0) q[(phase + 2) & 3] = gridDim.x;
+    nxt = blockIdx.x;
+  }
+  __device__ __forceinline__ int next(int items) {   // also the barrier that frees the staging buffers
+    int* slot = s_next + (round & 1);
+    if (threadIdx.x == 0) *slot = nxt;
+    __syncthreads();
+    ++round;
+    const int w = *slot;
+    if (w < items && threadIdx.x == 0) nxt = atomicAdd(q + (phase & 3), 1);
+    return w;
+  }
+  __device__ __forceinline__ void end() { ++phase; }
+};
+
 #define BAND_ITEMS_LOOP                                                        \
   const Geom<real>& g = A.g;                                                   \
   real* X = smem;                                                              \
@@ -246,14 +271,19 @@ __device__ __forceinline__ void band_of(const Geom<real>& g, int w, long long c_
   const int items = (int)(c_hi - c_lo) * g.tiles;                              \
   const long long pall = A.C * g.tiles;                                        \
   (void)X; (void)T; (void)pall;                                                \
-  for (int w = blockIdx.x; w < items; w += gridDim.x)
+  sched.begin();                                                               \
+  for (int w; (w = sched.next(items)) < items || (sched.end(), false);)
 
 // ---------------------------------------------------------------- P0: optb = sigma H^T b
 template <typename real, int NT, int RB, int W>
 __device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real* wx, const real* wy) {
   const long long c_lo = 0, c_hi = A.b_stride ? A.C : 1;
   const int hi_y = A.g.lo_y + NT - 1;
-  BAND_ITEMS_LOOP {
+  const Geom<real>& g = A.g;
+  real* T = smem + Band<real, NT, RB>::XROWS * A.pitch;
+  const int pitch = A.pitch;
+  const int items = (int)(c_hi - c_lo) * g.tiles;
+  for (int w = blockIdx.x; w < items; w += gridDim.x) {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     __syncthreads();
@@ -272,7 +302,7 @@ __device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real* wx, 
 
 // ---------------------------------------------------------------- P1: rhs, u = rhs - Op1 warm
 template <typename real, int NT, int RB, int W>
-__device__ void band_primal_init(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
+__device__ void band_primal_init(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, real* smem, double* red,
                                  const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
@@ -352,7 +382,7 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, long long c_lo, long 
 
 // ---------------------------------------------------------------- P2: v = Op1 (su * u); w = v
 template <typename real, int NT, int RB, int W>
-__device__ void band_v0(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
+__device__ void band_v0(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, real* smem, double* red,
                         const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
@@ -389,7 +419,7 @@ __device__ void band_v0(const UlpdaArgs<real>& A, long long c_lo, long long c_hi
 
 // ---------------------------------------------------------------- Ka: [deferred x, w update]; u = Op1 v - alfa u
 template <typename real, int NT, int RB, int W>
-__device__ void band_ka(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
+__device__ void band_ka(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, real* smem, double* red,
                         const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
@@ -453,7 +483,7 @@ __device__ void band_ka(const UlpdaArgs<real>& A, long long c_lo, long long c_hi
 
 // ---------------------------------------------------------------- Kb: v = Op1 u - beta v
 template <typename real, int NT, int RB, int W>
-__device__ void band_kb(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, real* smem, double* red,
+__device__ void band_kb(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, real* smem, double* red,
                         const real* wx, const real* wy) {
   constexpr int E = NT - 1;
   BAND_ITEMS_LOOP {
@@ -491,7 +521,7 @@ __device__ void band_kb(const UlpdaArgs<real>& A, long long c_lo, long long c_hi
 
 // ---------------------------------------------------------------- Pf: last deferred update, noise, xhat, statistics
 template <typename real, int RB>
-__device__ void band_primal_final(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, long long n) {
+__device__ void band_primal_final(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, long long n) {
   const Geom<real>& g = A.g;
   const int items = (int)(c_hi - c_lo) * g.tiles;
   const int quads_per_row = (g.nx + 3) / 4;
@@ -500,7 +530,8 @@ __device__ void band_primal_final(const UlpdaArgs<real>& A, long long c_lo, long
   const real inv_cnt = real(1) / (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
   const real cntn = (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
   (void)inv_cnt;
-  for (int w = blockIdx.x; w < items; w += gridDim.x) {
+  sched.begin();
+  for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     const LsqrState s = A.st[chain];
@@ -543,10 +574,11 @@ __device__ void band_primal_final(const UlpdaArgs<real>& A, long long c_lo, long
 
 // ---------------------------------------------------------------- Pd: y = proxdual(y + mu G xhat)
 template <typename real, int RB>
-__device__ void band_dual(const UlpdaArgs<real>& A, long long c_lo, long long c_hi, long long n) {
+__device__ void band_dual(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, long long n) {
   const Geom<real>& g = A.g;
   const int items = (int)(c_hi - c_lo) * g.tiles;
-  for (int w = blockIdx.x; w < items; w += gridDim.x) {
+  sched.begin();
+  for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     const real* xh = A.xhat + chain * g.P;
@@ -590,7 +622,10 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
   __shared__ double red[2 * BAND_NW];
+  __shared__ int s_next[2];
   cg::grid_group grid = cg::this_grid();
+  BandSched sched{A.queue, s_next, 0, 0, 0};
+  if (blockIdx.x == 0 && threadIdx.x < 4) A.queue[threadIdx.x] = gridDim.x;   // visible after the first grid barrier
   // the taps stay in the kernel-parameter constant bank: FFMA reads them as c[0][..] operands, no registers
   const real* wx = A.g.wx;
   const real* wy = A.g.wy;
@@ -606,35 +641,35 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid
     const long long c_hi = (c_lo + A.group < A.C) ? c_lo + A.group : A.C;
     for (long long n = 0; n < A.N; ++n) {
       if (A.mode == 0 && A.gfirst) {
-        band_dual<real, RB>(A, c_lo, c_hi, n);
+        band_dual<real, RB>(A, sched, c_lo, c_hi, n);
         grid.sync();
       }
       if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-      band_primal_init<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
+      band_primal_init<real, NT, RB, W>(A, sched, c_lo, c_hi, smem, red, wx, wy);
       grid.sync();
       phase_s1(A, c_lo, c_hi);
       grid.sync();
-      band_v0<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
+      band_v0<real, NT, RB, W>(A, sched, c_lo, c_hi, smem, red, wx, wy);
       grid.sync();
       phase_s2(A, c_lo, c_hi);
       grid.sync();
       while (*(volatile int*)A.n_active != 0) {
         grid.sync();   // everyone has read n_active before it is reset
         if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-        band_ka<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
+        band_ka<real, NT, RB, W>(A, sched, c_lo, c_hi, smem, red, wx, wy);
         grid.sync();
         phase_sa(A, c_lo, c_hi);
         grid.sync();
-        band_kb<real, NT, RB, W>(A, c_lo, c_hi, smem, red, wx, wy);
+        band_kb<real, NT, RB, W>(A, sched, c_lo, c_hi, smem, red, wx, wy);
         grid.sync();
         phase_sb(A, c_lo, c_hi);
         grid.sync();
       }
       if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(A.counters + 2, (unsigned long long)(c_hi - c_lo));
-      band_primal_final<real, RB>(A, c_lo, c_hi, n);
+      band_primal_final<real, RB>(A, sched, c_lo, c_hi, n);
       grid.sync();
       if (A.mode == 0 && !A.gfirst) {
-        band_dual<real, RB>(A, c_lo, c_hi, n);
+        band_dual<real, RB>(A, sched, c_lo, c_hi, n);
         grid.sync();
       }
     }
