@@ -177,6 +177,12 @@ typedef struct lmc_img_io {
   int64_t burnin;           /* global iterations excluded from mean/m2 */
   int64_t stat_count0;      /* samples already folded into mean/m2 (chunked runs) */
   uint64_t iter_offset;     /* global index of this call's first iteration (Philox counter) */
+  /* Non-convex data terms (algs.L2_ncvx_tv, algs.py:22-291): the Moreau-envelope term is evaluated by the
+   * unit entry points below between launches, so both need N == 1 (and gfirst == 0 for ULPDA).
+   * Streaming / band kernels only (not lmc_img_myula_run_onchip). */
+  const void* d_fgrad_extra; /* (C,P) MYULA: grad f(x) = sigma H^T(Hx - b) + fgrad_scale * this  (algs.py:283-291) */
+  double fgrad_scale;        /* -lamda */
+  const void* d_prox_arg;    /* (C,P) ULPDA: replaces x - tau (G^T y + z) as the argument of the L2 prox (algs.py:224-256) */
 } lmc_img_io;
 
 size_t lmc_img_myula_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C);
@@ -228,6 +234,20 @@ int lmc_img_l2_prox(const lmc_img_problem* pb, int dtype, double tau, int32_t it
                     void* stream);                                /* pyproximal.L2.prox (LSQR, warm start) */
 int lmc_img_noise(int dtype, int32_t ny, int32_t nx, int64_t C, int64_t N, uint64_t seed, uint64_t chain_offset,
                   uint64_t iter_offset, void* d_out, void* stream); /* test hook: the Philox normals (C,N,P) */
+
+/* Pieces of algs.L2_ncvx_tv, batched over C images, d_in != d_out:
+ * lmc_img_mctv_grad   MC-TV (Op2 = Gradient): m = G^T(w(Gx) Gx), isotropic: w = min(1/gamma, 1/|Gx|_2) per pixel
+ *                     (|Gx| = 0 read as 1e-9, algs.py:211-213,273-275); anisotropic: w Gx = Gx - soft(Gx, gamma)
+ *                     (algs.py:215-217,277).  out = base * x + scale * (m / post_div).
+ * lmc_img_metv_combine ME-TV (Op2 = None): d = x - p with p = TV_1.prox(x, gamma) from lmc_img_tv_prox;
+ *                     out = base * x + (den != 0 ? d / den : scale * d)   (algs.py:221-223, 280-282).
+ * lmc_img_pd_arg      out = x - tau * (G^T y + z): the primal argument of ULPDA (algs.py:436-446); d_z may be NULL. */
+int lmc_img_mctv_grad(int dtype, int32_t ny, int32_t nx, double gamma, int isotropic, double base, double scale,
+                      double post_div, int64_t C, const void* d_x, void* d_out, void* stream);
+int lmc_img_metv_combine(int dtype, int64_t n, double base, double scale, double den, const void* d_x,
+                         const void* d_p, void* d_out, void* stream);
+int lmc_img_pd_arg(int dtype, int32_t ny, int32_t nx, double tau, int64_t C, const void* d_x, const void* d_y,
+                   const void* d_z, void* d_out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -82,7 +82,8 @@ class ImgIo(C.Structure):
                 ("d_z", C.c_void_p), ("d_noise", C.c_void_p), ("d_samples", C.c_void_p),
                 ("d_ysamples", C.c_void_p), ("d_mean", C.c_void_p), ("d_m2", C.c_void_p),
                 ("d_counters", C.c_void_p), ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
-                ("burnin", C.c_int64), ("stat_count0", C.c_int64), ("iter_offset", C.c_uint64)]
+                ("burnin", C.c_int64), ("stat_count0", C.c_int64), ("iter_offset", C.c_uint64),
+                ("d_fgrad_extra", C.c_void_p), ("fgrad_scale", C.c_double), ("d_prox_arg", C.c_void_p)]
 
 
 # name -> (restype, argtypes); must list every symbol include/lmc_b200.h declares
@@ -120,6 +121,12 @@ SIGNATURES = {
                                   C.c_void_p, C.c_size_t, C.c_void_p]),
     "lmc_img_noise": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_uint64, C.c_uint64,
                                 C.c_uint64, C.c_void_p, C.c_void_p]),
+    "lmc_img_mctv_grad": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_int, C.c_double, C.c_double,
+                                    C.c_double, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lmc_img_metv_combine": (C.c_int, [C.c_int, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lmc_img_pd_arg": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_int64, C.c_void_p, C.c_void_p,
+                                 C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

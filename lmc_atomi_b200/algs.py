@@ -48,9 +48,24 @@ def _blur_of(proxf):
 
 
 def _engine(proxf, dtype):
-    _require(_kind(proxf) == "L2", f"proxf of type {_kind(proxf)}; supported: pyproximal.L2")
+    _require(_kind(proxf) in ("L2", "L2_ncvx_tv"),
+             f"proxf of type {_kind(proxf)}; supported: pyproximal.L2, algs.L2_ncvx_tv")
     dims, h = _blur_of(proxf)
     return imaging.DeconvEngine(dims, h, np.asarray(proxf.b, dtype=np.float64), float(proxf.sigma), dtype=dtype)
+
+
+def _moreau_term(proxf, dims):
+    """None for pyproximal.L2; the MC-TV / ME-TV term of an L2_ncvx_tv (algs.py:164-170)."""
+    if _kind(proxf) != "L2_ncvx_tv":
+        return None
+    _require(tuple(int(d) for d in proxf.dims) == tuple(dims), "L2_ncvx_tv dims must equal the image dims")
+    _require(isinstance(proxf.niter, int), "callable niter")
+    _require(getattr(proxf, "densesolver", None) is None, "dense solvers")
+    if proxf.Op2 is not None:
+        _require(_is_gradient(proxf.Op2, dims), "Op2 must be pylops.Gradient(dims, kind='forward', edge=False)")
+        return imaging.MoreauTerm("mc", proxf.lamda, proxf.gamma, bool(proxf.isotropic))
+    _require(bool(proxf.isotropic), "ME-TV with the 1-D TV of algs.py:170")
+    return imaging.MoreauTerm("me", proxf.lamda, proxf.gamma, True, int(proxf.niter), float(proxf.rtol))
 
 
 def _chunk(niter, P, itemsize, arrays):
@@ -72,6 +87,7 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
     _require(_kind(proxg) == "TV", f"proxg of type {_kind(proxg)}; supported: pyproximal.TV")
     eng = _engine(proxf, dtype)
     torch = eng.torch
+    ncvx = _moreau_term(proxf, eng.dims)
     _require(tuple(int(d) for d in proxg.dims) == eng.dims, "TV dims must equal the image dims")
     x0 = np.asarray(x0, dtype=np.float64)
     P = eng.P
@@ -94,7 +110,7 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
         noise = None if philox else rng.standard_normal((1, n, P))
         samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
         keep = eng.myula(x, n, tau, gamma, float(proxg.sigma), int(proxg.niter), float(proxg.rtol),
-                         epsg=float(epsg), seed=seed, noise=noise, samples=samples, iter_offset=done)
+                         epsg=float(epsg), seed=seed, noise=noise, samples=samples, iter_offset=done, ncvx=ncvx)
         out[done:done + n] = samples[0].double().cpu().numpy()   # synchronises the stream
         del keep
         if per_iter:
@@ -129,6 +145,7 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
     eng = _engine(proxf, dtype)
     torch = eng.torch
     P = eng.P
+    ncvx = _moreau_term(proxf, eng.dims)
     _require(_kind(proxg) in ("L21", "L1"), f"proxg of type {_kind(proxg)}; supported: pyproximal.L21, L1")
     iso = _kind(proxg) == "L21"
     _require(not iso or int(getattr(proxg, "ndim", 2)) == 2, "L21 with ndim != 2")
@@ -170,7 +187,7 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
         keep = eng.ulpda(x, xhat, y, warm, n, float(tau[done]), float(mu[done]), float(theta), float(proxg.sigma),
                          iso, gfirst, int(proxf.niter), warm_start=warm_on, atol=kw.get("atol", 1e-6),
                          btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=z, seed=seed, noise=noise,
-                         samples=samples, ysamples=ys, iter_offset=done)
+                         samples=samples, ysamples=ys, iter_offset=done, ncvx=ncvx)
         out[done:done + n] = samples[0].double().cpu().numpy()
         if need_y:
             yh = ys[0].double().cpu().numpy().reshape(n, 2 * P)
@@ -203,9 +220,10 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
 
 
 class L2_ncvx_tv:
-    """Parameter carrier for the reference's non-convex data term (algs.py:22-291):
-    sigma/2 ||Op x - b||^2 - lamda * env_gamma(TV)(x), MC-TV when ``Op2`` (the Gradient) is given,
-    ME-TV otherwise.  Same constructor as algs.py:129-131.  The samplers read its parameters."""
+    """The reference's non-convex data term (algs.py:22-291):
+    sigma/2 ||Op x - b||^2 - lamda * env_gamma(TV)(x), MC-TV when ``Op2`` (the Gradient) is given, ME-TV
+    otherwise.  Same constructor as algs.py:129-131.  The samplers read its parameters; ``grad``, ``prox`` and
+    ``__call__`` evaluate on the GPU with the same unit kernels the samplers use."""
 
     def __init__(self, dims, Op=None, Op2=None, b=None, q=None, sigma=1., alpha=1., lamda=1., gamma=.5,
                  qgrad=True, isotropic=False, niter=10, rtol=1e-4, x0=None, warm=True, densesolver=None,
@@ -217,3 +235,65 @@ class L2_ncvx_tv:
         self.x0, self.warm, self.densesolver, self.count = x0, warm, densesolver, 0
         self.kwargs_solver = {} if kwargs_solver is None else kwargs_solver
         self.hasgrad = True
+        self._eng = None
+
+    def _engine64(self):
+        if self._eng is None:
+            self._eng = _engine(self, "float64")
+        return self._eng
+
+    def _dev(self, x):
+        eng = self._engine64()
+        return eng.torch.as_tensor(np.asarray(x, dtype=np.float64)).to(eng.dev).reshape(1, -1).contiguous()
+
+    def grad_moreau(self, x):
+        """algs.py:270-282."""
+        eng = self._engine64()
+        out = imaging.moreau_apply(eng.dims, self._dev(x), _moreau_term(self, eng.dims))
+        return out.cpu().numpy().reshape(np.shape(x))
+
+    def grad(self, x):
+        """sigma Op^H (Op x - b) - lamda grad_moreau(x)   (algs.py:270-291)."""
+        eng = self._engine64()
+        xd = self._dev(x)
+        r = imaging.blur(eng.spec, xd) - eng.b
+        g = (self.sigma * imaging.blur(eng.spec, r, adjoint=True)).cpu().numpy().reshape(np.shape(x))
+        return g - self.lamda * self.grad_moreau(x)
+
+    def prox(self, x, tau):
+        """algs.py:201-267: x += tau lamda grad_moreau(x) IN PLACE (as the reference does), then the LSQR solve."""
+        eng = self._engine64()
+        torch = eng.torch
+        self.count += 1
+        term = _moreau_term(self, eng.dims)
+        arg = imaging.moreau_apply(eng.dims, self._dev(x), term, tau=float(tau))
+        if isinstance(x, np.ndarray) and x.dtype == np.float64:
+            x[...] = arg.cpu().numpy().reshape(x.shape)
+        warm = self._dev(self.x0).clone() if (self.x0 is not None and self.warm) else \
+            torch.zeros((1, eng.P), dtype=torch.float64, device=eng.dev)
+        kw = self.kwargs_solver
+        out = eng.l2_prox(arg, tau, warm, iter_lim=int(self.niter), atol=kw.get("atol", 1e-6),
+                          btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8))
+        out = out.cpu().numpy().reshape(np.shape(x))
+        if self.warm:
+            self.x0 = out
+        return out
+
+    def __call__(self, x):
+        """f(x) = sigma/2 ||Op x - b||^2 - lamda env_gamma(x)   (algs.py:173-190)."""
+        eng = self._engine64()
+        torch = eng.torch
+        xd = self._dev(x)
+        r = imaging.blur(eng.spec, xd) - eng.b
+        f = float(self.sigma / 2.0 * r.pow(2).sum().item())
+        g = float(self.gamma)
+        if self.Op2 is not None:
+            d = imaging.grad(eng.dims, xd)[0]                    # (2,P)
+            v = d.pow(2).sum(dim=0).sqrt() if self.isotropic else d.reshape(-1)
+            mp = torch.sign(v) * torch.clamp(v.abs() - g, min=0.0)   # L1(1).prox(v, gamma)
+            env = float((mp.abs().sum() + (v - mp).pow(2).sum() / (2 * g)).item())
+        else:
+            mp = imaging.tv_prox(eng.dims, xd, g, int(self.niter), float(self.rtol))
+            dg = imaging.grad(eng.dims, mp)[0]
+            env = float((dg.pow(2).sum(dim=0).sqrt().sum() + (xd - mp).pow(2).sum() / (2 * g)).item())
+        return f - self.lamda * env

@@ -51,6 +51,8 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
     A.samples = (real*)io->d_samples;
     A.mean = (real*)io->d_mean;
     A.m2 = (real*)io->d_m2;
+    A.gextra = (const real*)io->d_fgrad_extra;
+    A.gscale = (real)io->fgrad_scale;
     A.sigma_l2 = (real)pb->sigma_l2;
     A.tau = (real)pr->tau;
     A.a_x = (real)(1 - pr->tau / pr->gamma);
@@ -87,6 +89,7 @@ extern "C" int lmc_img_myula_run(const lmc_img_problem* pb, const lmc_img_myula_
   LMC_REQUIRE(io->d_x != nullptr && pb->d_b != nullptr, "lmc_img_myula_run: d_x and d_b are required");
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_myula_run: b_chain_stride must be 0 or ny*nx");
+  LMC_REQUIRE(io->d_fgrad_extra == nullptr || N == 1, "lmc_img_myula_run: d_fgrad_extra needs N == 1");
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64 ? run_myula<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st)
                           : run_myula<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st);

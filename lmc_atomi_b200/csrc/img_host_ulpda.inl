@@ -125,6 +125,7 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
     A.g_sigma = (real)pr->g_sigma;
     A.isotropic = pr->g_isotropic;
     A.gfirst = pr->gfirst;
+    A.in = (const real*)io->d_prox_arg;
   } else {
     A.in = (const real*)prox_in;
     A.out = (real*)prox_out;
@@ -160,6 +161,8 @@ extern "C" int lmc_img_ulpda_run(const lmc_img_problem* pb, const lmc_img_ulpda_
               "lmc_img_ulpda_run: d_x, d_xhat, d_y, d_warm and d_b are required");
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_ulpda_run: b_chain_stride must be 0 or ny*nx");
+  LMC_REQUIRE(io->d_prox_arg == nullptr || (N == 1 && !pr->gfirst),
+              "lmc_img_ulpda_run: d_prox_arg needs N == 1 and gfirst == 0");
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64 ? run_ulpda<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st)
                           : run_ulpda<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st);
@@ -187,6 +190,8 @@ extern "C" int lmc_img_ulpda_run_band(const lmc_img_problem* pb, const lmc_img_u
               "lmc_img_ulpda_run_band: d_x, d_xhat, d_y, d_warm and d_b are required");
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_ulpda_run_band: b_chain_stride must be 0 or ny*nx");
+  LMC_REQUIRE(io->d_prox_arg == nullptr || (N == 1 && !pr->gfirst),
+              "lmc_img_ulpda_run_band: d_prox_arg needs N == 1 and gfirst == 0");
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64
              ? run_ulpda<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true, group)

@@ -33,6 +33,8 @@ struct MyulaArgs {
   const real* b;
   long long b_stride;
   real* grad;
+  const real* gextra;  // optional (C,P): grad f += gscale * gextra (non-convex data term)
+  real gscale;
   real* D;            // [3][2][C][P]
   const real* noise;  // [C][N][P] or null
   real* samples;      // [C][N][P] or null
@@ -283,7 +285,9 @@ __device__ void phase_update(const MyulaArgs<real>& A, long long n, real* smem) 
         }
         real xi = (A.noise != nullptr) ? A.noise[(chain * A.N + n) * g.P + o] : z[k];
         // algs.py:569: (1 - tau/gamma) x - tau grad f(x) + tau/gamma prox_g(x) + sqrt(2 tau) xi
-        real xn = A.a_x * xv - A.tau * A.grad[chain * g.P + o] + A.tog * sol + A.s2t * xi;
+        real gr = A.grad[chain * g.P + o];
+        if (A.gextra != nullptr) gr = gr + A.gscale * A.gextra[chain * g.P + o];   // algs.py:291: g - lamda * grad_moreau
+        real xn = A.a_x * xv - A.tau * gr + A.tog * sol + A.s2t * xi;
         xc[o] = xn;
         if (A.samples != nullptr) A.samples[(chain * A.N + n) * g.P + o] = xn;
         if (stats) {

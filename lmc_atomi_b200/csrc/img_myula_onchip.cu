@@ -600,6 +600,7 @@ extern "C" int lmc_img_myula_run_onchip(const lmc_img_problem* pb, const lmc_img
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_myula_run_onchip: b_chain_stride must be 0 or ny*nx");
   LMC_REQUIRE(io->d_counters != nullptr, "lmc_img_myula_run_onchip: d_counters is required");
+  LMC_REQUIRE(io->d_fgrad_extra == nullptr, "lmc_img_myula_run_onchip: d_fgrad_extra is not supported (use lmc_img_myula_run)");
   OcArgs A;
   memset(&A, 0, sizeof(A));
   fill_geom(pb, A.g);

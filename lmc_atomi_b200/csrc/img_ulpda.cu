@@ -51,7 +51,7 @@ struct UlpdaArgs {
   real* ysamples;
   real* mean;
   real* m2;
-  const real* in;   // l2-prox mode: argument
+  const real* in;   // l2-prox mode: argument; ULPDA mode: optional override of x - tau (G^T y + z)
   real* out;        // l2-prox mode: result
   double* partial;  // [3][C][tiles]
   LsqrState* st;
@@ -157,7 +157,7 @@ __device__ void phase_primal_init(const UlpdaArgs<real>& A, real* smem, double* 
       if (i < g.ny && j < g.nx) {
         long long o = (long long)i * g.nx + j;
         real arg;
-        if (A.mode == 1) {
+        if (A.in != nullptr) {   // L2-prox mode, or the non-convex data term's pre-processed argument
           arg = A.in[chain * g.P + o];
         } else {
           // G^T y in the accumulation order of pylops (axis 0 then axis 1); v[last] is never read

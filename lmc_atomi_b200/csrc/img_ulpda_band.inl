@@ -318,7 +318,7 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, BandSched& sched, lon
     // operands of the pointwise part: [0] arg = x - tau (G^T y + z)  (or the prox argument), [1] sigma H^T b
     auto pre = [&](int i, int c, Pack<real, W> (&v)[2]) {
       const int o = i * g.nx + c;
-      if (A.mode == 1) {
+      if (A.in != nullptr) {
         v[0] = ldp<real, W>(inC + o);
       } else {
         // G^T y in the accumulation order of pylops (axis 0 then axis 1); v[last] is never read

@@ -73,7 +73,7 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
 
     def launch():
         state["keep"] = eng.myula(x, iters, tau, gamma, TAU_REG, 10, 1e-4, seed=0, mean=mean,
-                                  iter_offset=state["it"], stat_count0=state["it"], engine=engine)
+                                  iter_offset=state["it"], engine=engine)
         state["it"] += iters
 
     for _ in range(2):      # burn-in so that the TV early exit is in its steady regime
@@ -126,7 +126,7 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
 
     def launch():
         state["keep"] = eng.ulpda(x, xhat, y, warm, iters, tau, mu, 1.0, TAU_REG, True, False, 50, seed=0,
-                                  mean=mean, iter_offset=state["it"], stat_count0=state["it"], engine=engine,
+                                  mean=mean, iter_offset=state["it"], engine=engine,
                                   group=group)
         state["it"] += iters
 

@@ -160,6 +160,68 @@ def tv_prox(dims, x, gamma, niter=10, rtol=1e-4, counters=None):
     return out.reshape(x.shape)
 
 
+
+class MoreauTerm:
+    """The concave part ``-lamda * env_gamma(TV)`` of the reference's ``algs.L2_ncvx_tv`` (algs.py:22-291):
+    ``kind`` "mc" = MC-TV (Op2 = Gradient; isotropic or not), "me" = ME-TV (inner TV(dims, 1, niter, rtol))."""
+
+    def __init__(self, kind, lamda, gamma, isotropic=True, niter=50, rtol=1e-4):
+        if kind not in ("mc", "me"):
+            raise ValueError("kind must be 'mc' or 'me'")
+        if kind == "me" and not isotropic:
+            raise NotImplementedError("ME-TV with the 1-D TV of algs.py:170 has no CUDA path (the driver never uses it)")
+        self.kind, self.lamda, self.gamma = kind, float(lamda), float(gamma)
+        self.isotropic, self.niter, self.rtol = bool(isotropic), int(niter), float(rtol)
+
+
+def moreau_apply(dims, x, term: MoreauTerm, tau=None, counters=None):
+    """``tau is None``: grad_moreau(x) (algs.py:270-282).  Otherwise the in-place pre-step of
+    ``L2_ncvx_tv.prox``: x + tau*lamda*grad_moreau(x), with the reference's grouping of the scalars
+    (algs.py:208-223).  Device tensors (C,P); returns a new tensor."""
+    torch = _lib.require_cuda()
+    lib = _lib.load()
+    P = dims[0] * dims[1]
+    x2 = x.reshape(-1, P).contiguous()
+    out = torch.empty_like(x2)
+    dt = _dt("float64" if x2.dtype == torch.float64 else "float32")
+    g = term.gamma
+    if term.kind == "mc":
+        if tau is None:
+            base, scale, post = 0.0, 1.0, (1.0 if term.isotropic else g)
+        else:
+            base, post = 1.0, 1.0
+            scale = tau * term.lamda if term.isotropic else tau * term.lamda / g
+        with torch.cuda.device(x2.device):
+            rc = lib.lmc_img_mctv_grad(dt, dims[0], dims[1], g, 1 if term.isotropic else 0, base, scale, post,
+                                       x2.shape[0], x2.data_ptr(), out.data_ptr(), _stream(torch, x2.device))
+        _lib.check(rc, "lmc_img_mctv_grad")
+    else:
+        p = tv_prox(dims, x2, g, term.niter, term.rtol, counters)
+        if tau is None:
+            base, scale, den = 0.0, 0.0, g
+        else:
+            base, scale, den = 1.0, tau * term.lamda / g, 0.0
+        with torch.cuda.device(x2.device):
+            rc = lib.lmc_img_metv_combine(dt, x2.numel(), base, scale, den, x2.data_ptr(), p.data_ptr(),
+                                          out.data_ptr(), _stream(torch, x2.device))
+        _lib.check(rc, "lmc_img_metv_combine")
+        torch.cuda.current_stream(x2.device).synchronize()   # p lifetime
+    return out.reshape(x.shape)
+
+
+def pd_arg(dims, x, y, tau, z=None):
+    """x - tau * (G^T y + z): the argument ULPDA hands to proxf.prox (algs.py:436-446)."""
+    torch = _lib.require_cuda()
+    lib = _lib.load()
+    out = torch.empty_like(x)
+    dt = _dt("float64" if x.dtype == torch.float64 else "float32")
+    with torch.cuda.device(x.device):
+        rc = lib.lmc_img_pd_arg(dt, dims[0], dims[1], float(tau), x.shape[0], x.data_ptr(), y.data_ptr(),
+                                z.data_ptr() if z is not None else None, out.data_ptr(), _stream(torch, x.device))
+    _lib.check(rc, "lmc_img_pd_arg")
+    return out
+
+
 def philox_image_noise(dims, C_, N, seed, chain_offset=0, iter_offset=0, dtype="float32", device=None):
     """The N(0,1) draws the samplers generate in-kernel, as a (C,N,P) device tensor."""
     torch = _lib.require_cuda()
@@ -267,8 +329,37 @@ class DeconvEngine:
 
     def myula(self, x, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, epsg=1.0, seed=0, chain_offset=0,
               noise=None, samples=None, mean=None, m2=None, burnin=0, stat_count0=0, iter_offset=0,
-              engine="auto"):
+              engine="auto", ncvx=None):
         """Advances the (C,P) device tensor ``x`` in place by N MYULA iterations (algs.py:564-583).
+
+        ``ncvx``: a MoreauTerm makes the data term the reference's L2_ncvx_tv (MC-TV / ME-TV): every iteration
+        evaluates grad_moreau(x) with the unit kernels of csrc/img_ncvx.cu and hands it to a one-iteration
+        launch of the streaming kernel (grad f = sigma H^T(Hx - b) - lamda grad_moreau(x), algs.py:283-291)."""
+        if ncvx is None:
+            return self._myula_launch(x, N, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, noise,
+                                      samples, mean, m2, burnin, stat_count0, iter_offset, engine)
+        if engine == "onchip":
+            raise NotImplementedError("the on-chip MYULA kernel has no non-convex data term; use engine='stream'")
+        torch = self.torch
+        Cn = x.shape[0]
+        nz = self._noise(noise, Cn, N)
+        keep = None
+        for n in range(int(N)):
+            gm = moreau_apply(self.dims, x, ncvx, counters=None)
+            nzn = nz[:, n:n + 1].contiguous() if nz is not None else None
+            sn = torch.empty((Cn, 1, self.P), dtype=self.tdt, device=self.dev) if samples is not None else None
+            keep = self._myula_launch(x, 1, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, nzn, sn,
+                                      mean, m2, burnin, stat_count0, iter_offset + n, "stream", fgrad_extra=gm,
+                                      fgrad_scale=-ncvx.lamda)
+            torch.cuda.current_stream(self.dev).synchronize()   # gm / workspace lifetime
+            if samples is not None:
+                samples[:, n] = sn[:, 0]
+        return keep
+
+    def _myula_launch(self, x, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, epsg=1.0, seed=0, chain_offset=0,
+                      noise=None, samples=None, mean=None, m2=None, burnin=0, stat_count0=0, iter_offset=0,
+                      engine="auto", fgrad_extra=None, fgrad_scale=0.0):
+        """One launch: N iterations of all chains.
 
         ``engine``: "onchip" = cluster kernel with the chain state in shared memory (fp32, images up to
         256 x 256), "stream" = tiled kernel through HBM (any size, fp32/fp64), "auto" = on-chip when
@@ -280,7 +371,7 @@ class DeconvEngine:
         pr.tv_sigma, pr.tv_rtol, pr.tv_niter = float(tv_sigma), float(tv_rtol), int(tv_niter)
         if engine not in ("auto", "onchip", "stream"):
             raise ValueError("engine must be 'auto', 'onchip' or 'stream'")
-        onchip = engine == "onchip" or (engine == "auto" and self.onchip_supported())
+        onchip = engine == "onchip" or (engine == "auto" and self.onchip_supported() and fgrad_extra is None)
         if onchip:
             ws = torch.empty(256, dtype=torch.uint8, device=self.dev)
         else:
@@ -289,6 +380,8 @@ class DeconvEngine:
         nz = self._noise(noise, Cn, N)
         io = self._io(Cn, N, nz, samples, mean, m2, burnin, stat_count0, iter_offset, ws)
         io.d_x = x.data_ptr()
+        if fgrad_extra is not None:
+            io.d_fgrad_extra, io.fgrad_scale = fgrad_extra.data_ptr(), float(fgrad_scale)
         pb = self._problem()
         fn, name = ((lib.lmc_img_myula_run_onchip, "lmc_img_myula_run_onchip") if onchip
                     else (lib.lmc_img_myula_run, "lmc_img_myula_run"))
@@ -302,8 +395,44 @@ class DeconvEngine:
     def ulpda(self, x, xhat, y, warm, N, tau, mu, theta=1.0, g_sigma=1.0, isotropic=True, gfirst=True,
               lsqr_iter_lim=50, warm_start=True, atol=1e-6, btol=1e-6, conlim=1e8, z=None, seed=0,
               chain_offset=0, noise=None, samples=None, ysamples=None, mean=None, m2=None, burnin=0,
-              stat_count0=0, iter_offset=0, engine="auto", group=0):
+              stat_count0=0, iter_offset=0, engine="auto", group=0, ncvx=None):
         """Advances (x, xhat, y, warm) in place by N ULPDA iterations (algs.py:432-467).
+
+        ``ncvx``: a MoreauTerm makes proxf the reference's L2_ncvx_tv: every iteration forms the primal argument
+        x - tau (G^T y + z), adds tau*lamda*grad_moreau of it (algs.py:208-223) with the unit kernels of
+        csrc/img_ncvx.cu and hands the result to a one-iteration launch (gfirst=False only)."""
+        if ncvx is None:
+            return self._ulpda_launch(x, xhat, y, warm, N, tau, mu, theta, g_sigma, isotropic, gfirst, lsqr_iter_lim,
+                                      warm_start, atol, btol, conlim, z, seed, chain_offset, noise, samples, ysamples,
+                                      mean, m2, burnin, stat_count0, iter_offset, engine, group)
+        if gfirst:
+            raise NotImplementedError("L2_ncvx_tv with gfirst=True has no CUDA path (the driver uses gfirst=False)")
+        torch = self.torch
+        Cn = x.shape[0]
+        nz = self._noise(noise, Cn, N)
+        zt = torch.as_tensor(z).to(self.dev, self.tdt).reshape(self.P).contiguous() if z is not None else None
+        keep = None
+        for n in range(int(N)):
+            arg = pd_arg(self.dims, x, y, tau, zt)
+            arg = moreau_apply(self.dims, arg, ncvx, tau=float(tau))
+            nzn = nz[:, n:n + 1].contiguous() if nz is not None else None
+            sn = torch.empty((Cn, 1, self.P), dtype=self.tdt, device=self.dev) if samples is not None else None
+            ysn = torch.empty((Cn, 1, 2, self.P), dtype=self.tdt, device=self.dev) if ysamples is not None else None
+            keep = self._ulpda_launch(x, xhat, y, warm, 1, tau, mu, theta, g_sigma, isotropic, False, lsqr_iter_lim,
+                                      warm_start, atol, btol, conlim, None, seed, chain_offset, nzn, sn, ysn, mean, m2,
+                                      burnin, stat_count0, iter_offset + n, engine, group, prox_arg=arg)
+            torch.cuda.current_stream(self.dev).synchronize()
+            if samples is not None:
+                samples[:, n] = sn[:, 0]
+            if ysamples is not None:
+                ysamples[:, n] = ysn[:, 0]
+        return keep
+
+    def _ulpda_launch(self, x, xhat, y, warm, N, tau, mu, theta=1.0, g_sigma=1.0, isotropic=True, gfirst=True,
+                      lsqr_iter_lim=50, warm_start=True, atol=1e-6, btol=1e-6, conlim=1e8, z=None, seed=0,
+                      chain_offset=0, noise=None, samples=None, ysamples=None, mean=None, m2=None, burnin=0,
+                      stat_count0=0, iter_offset=0, engine="auto", group=0, prox_arg=None):
+        """One launch: N iterations of all chains.
 
         ``engine``: "band" = row-band kernel (fused two-pass blur, chains advanced in L2-sized groups of
         ``group`` chains, 0 = automatic), "tile" = 32x32-tile kernel (any separable filter), "auto" = band
@@ -325,6 +454,8 @@ class DeconvEngine:
             zt = torch.as_tensor(z).to(self.dev, self.tdt).reshape(self.P).contiguous()
             io.d_z = zt.data_ptr()
         io.d_ysamples = ysamples.data_ptr() if ysamples is not None else None
+        if prox_arg is not None:
+            io.d_prox_arg = prox_arg.data_ptr()
         pb = self._problem()
         if engine not in ("auto", "band", "tile"):
             raise ValueError("engine must be 'auto', 'band' or 'tile'")
