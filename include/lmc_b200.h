@@ -249,6 +249,17 @@ int lmc_img_metv_combine(int dtype, int64_t n, double base, double scale, double
 int lmc_img_pd_arg(int dtype, int32_t ny, int32_t nx, double tau, int64_t C, const void* d_x, const void* d_y,
                    const void* d_z, void* d_out, void* stream);
 
+/* Per-sample metrics on the device, replacing the reference's per-iteration host callback
+ * (prox_lmc_deconv.py:35-36,128-133): for each of the M images of d_x (M,P) -- e.g. the (C,N,P) samples of a
+ * run, images_per_chain = N -- d_out (M,4) doubles receives
+ *   [0] ||H x - b||^2, [1] sum_pixels |G x| (isotropic l2 / anisotropic l1), [2] ||x - x*||^2, [3] ||x*||^2
+ * (x* = d_xtrue (P,), may be NULL), from which cost = sigma_l2/2 [0] + g_sigma [1], err = sqrt([2]),
+ * SNR = 10 log10([3]/[2]), MSE = [2]/P, PSNR = 10 log10(255^2 / MSE).  fp64 sums, fixed order. */
+size_t lmc_img_metrics_workspace_bytes(int64_t M);
+int lmc_img_sample_metrics(const lmc_img_problem* pb, int dtype, int isotropic, int64_t M, int64_t images_per_chain,
+                           const void* d_x, const void* d_xtrue, double* d_out, void* d_workspace,
+                           size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,7 +21,27 @@ from numpy.random import default_rng
 
 from . import _lib, imaging
 
-__all__ = ["MoreauYosidaUnadjustedLangevin", "UnadjustedLangevinPrimalDual", "L2_ncvx_tv"]
+__all__ = ["MoreauYosidaUnadjustedLangevin", "UnadjustedLangevinPrimalDual", "L2_ncvx_tv", "DeviceMetrics"]
+
+
+class DeviceMetrics:
+    """Collects, on the GPU, what the driver's per-iteration host callback computes
+    (prox_lmc_deconv.py:128-133: cost f(x) + g(Kx), ||x - xtrue||, SNR, PSNR, MSE).  Pass an instance as
+    ``device_metrics=`` instead of ``callback=``: the sampler then runs its iterations in large launches and
+    reduces every sample to four sums on the device; after the run the lists ``cost``, ``err``, ``snr``,
+    ``psnr``, ``mse`` hold one value per iteration (f = L2 data term; g = proxg.sigma * TV / l1)."""
+
+    KEYS = ("cost", "err", "snr", "psnr", "mse")
+
+    def __init__(self, xtrue):
+        self.xtrue = np.asarray(xtrue, dtype=np.float64).ravel()
+        for k in self.KEYS:
+            setattr(self, k, [])
+
+    def _extend(self, res):
+        for k in self.KEYS:
+            getattr(self, k).extend(np.asarray(res[k], dtype=np.float64).ravel().tolist())
+
 
 CHUNK_BYTES = 1 << 30     # device staging for noise + samples per launch
 
@@ -78,7 +98,7 @@ def _show_line(iiter, niter):
 
 
 def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1., niter=10, seed=0,
-                                   callback=None, show=False, dtype="float64", philox=False):
+                                   callback=None, show=False, dtype="float64", philox=False, device_metrics=None):
     """MYULA (algs.py:477-587):
     x <- (1 - tau/gamma) x - tau grad f(x) + tau/gamma prox_{gamma epsg g}(x) + sqrt(2 tau) xi.
     Returns the (niter, P) float64 array of samples, as the reference does."""
@@ -111,6 +131,8 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
         samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
         keep = eng.myula(x, n, tau, gamma, float(proxg.sigma), int(proxg.niter), float(proxg.rtol),
                          epsg=float(epsg), seed=seed, noise=noise, samples=samples, iter_offset=done, ncvx=ncvx)
+        if device_metrics is not None:
+            device_metrics._extend(eng.sample_metrics(samples[0], device_metrics.xtrue, float(proxg.sigma), True))
         out[done:done + n] = samples[0].double().cpu().numpy()   # synchronises the stream
         del keep
         if per_iter:
@@ -138,7 +160,7 @@ def _is_gradient(A, dims):
 
 def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, theta=1., niter=10,
                                  seed=0, gfirst=True, callback=None, callbacky=False, returny=False,
-                                 show=False, dtype="float64", philox=False):
+                                 show=False, dtype="float64", philox=False, device_metrics=None):
     """ULPDA (algs.py:295-474) for U(x) = f(x) + x^T z + g(Ax) with f = L2 (prox by warm-started
     LSQR), g = L21 / L1 (dual prox = projection), A = forward-difference Gradient.
     Returns (niter, P) samples [and (niter, 2P) dual samples when ``returny``]."""
@@ -188,6 +210,8 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
                          iso, gfirst, int(proxf.niter), warm_start=warm_on, atol=kw.get("atol", 1e-6),
                          btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=z, seed=seed, noise=noise,
                          samples=samples, ysamples=ys, iter_offset=done, ncvx=ncvx)
+        if device_metrics is not None:
+            device_metrics._extend(eng.sample_metrics(samples[0], device_metrics.xtrue, float(proxg.sigma), iso))
         out[done:done + n] = samples[0].double().cpu().numpy()
         if need_y:
             yh = ys[0].double().cpu().numpy().reshape(n, 2 * P)

@@ -496,6 +496,42 @@ class DeconvEngine:
         torch.cuda.current_stream(self.dev).synchronize()
         return out.reshape(x.shape)
 
+    # ------------------------------------------------------------------ per-sample metrics on the device
+    def sample_metrics(self, x, xtrue=None, g_sigma=1.0, isotropic=True, images_per_chain=None):
+        """Cost / error / SNR / PSNR / MSE of every image of ``x`` ((M,P) or (C,N,P) device tensor) without
+        copying the images to the host: what the reference's per-iteration callback computes
+        (prox_lmc_deconv.py:35-36,128-133) for f = L2 and g = g_sigma * TV (isotropic) or g_sigma * ||G x||_1.
+        Returns a dict of float64 numpy arrays shaped like the leading dims of ``x``."""
+        torch, lib = self.torch, self.lib
+        lead = tuple(x.shape[:-1])
+        if images_per_chain is None:
+            images_per_chain = lead[1] if len(lead) == 2 else 1
+        x2 = x.reshape(-1, self.P).contiguous()
+        M = x2.shape[0]
+        xt = None
+        if xtrue is not None:
+            xt = torch.as_tensor(xtrue).to(self.dev, self.tdt).reshape(self.P).contiguous()
+        out = torch.empty((M, 4), dtype=torch.float64, device=self.dev)
+        nb = lib.lmc_img_metrics_workspace_bytes(M)
+        ws = torch.empty(nb, dtype=torch.uint8, device=self.dev)
+        pb = self._problem()
+        with torch.cuda.device(self.dev):
+            rc = lib.lmc_img_sample_metrics(C.byref(pb), _dt(self.dtype), 1 if isotropic else 0, M,
+                                            int(images_per_chain), x2.data_ptr(),
+                                            xt.data_ptr() if xt is not None else None, out.data_ptr(), ws.data_ptr(),
+                                            nb, _stream(torch, self.dev))
+        _lib.check(rc, "lmc_img_sample_metrics")
+        s = out.cpu().numpy().reshape(lead + (4,))     # synchronises; (M,4) doubles only
+        res = {"f": self.sigma_l2 / 2.0 * s[..., 0], "g": float(g_sigma) * s[..., 1]}
+        res["cost"] = res["f"] + res["g"]
+        if xtrue is not None:
+            with np.errstate(divide="ignore"):
+                res["err"] = np.sqrt(s[..., 2])
+                res["snr"] = 10.0 * np.log10(s[..., 3] / s[..., 2])
+                res["mse"] = s[..., 2] / self.P
+                res["psnr"] = 10.0 * np.log10(255.0 ** 2 / res["mse"])
+        return res
+
     # ------------------------------------------------------------------ many-chain production runs
     def run_myula(self, chains, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, seed=0, chain_offset=0,
                   burnin=0, x0=None, second_moment=True, sync=True, engine="auto") -> ImageStats:
