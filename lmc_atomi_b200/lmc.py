@@ -69,6 +69,21 @@ class LangevinMonteCarlo(MixtureSampler):
     def mla(self, gamma, beta):
         return self._reference_call("mla", gamma, beta=beta)
 
+    # ---- evaluation helpers of the driver (plot grids; host numpy, not on the sampler path) -----------
+    def multivariate_gaussian(self, theta, mu, Sigma):
+        """N(theta; mu, Sigma), broadcast over leading dims (lmc.py:39-44)."""
+        d = np.asarray(theta, dtype=np.float64) - mu
+        q = ((d @ np.linalg.inv(Sigma)) * d).sum(axis=-1)
+        return np.exp(-q / 2) / np.sqrt((2 * np.pi) ** self.d * np.abs(np.linalg.det(Sigma)))
+
+    def density_gaussian_mixture(self, theta):
+        """lmc.py:46-48."""
+        return sum(self.omegas[i] * self.multivariate_gaussian(theta, self.mus[i], self.Sigmas[i])
+                   for i in range(len(self.mus)))
+
+    def potential_gaussian_mixture(self, theta):
+        return -np.log(self.density_gaussian_mixture(theta))
+
     def true_samples(self):
         """Exact draws from the mixture (lmc.py:82-90).  Evaluation input, not part of
         the sampler hot path: plain host numpy with the reference's draw order."""
@@ -78,3 +93,39 @@ class LangevinMonteCarlo(MixtureSampler):
             i = rng.integers(0, len(self.mus))
             out[k] = rng.multivariate_normal(self.mus[i], self.Sigmas[i])
         return out
+
+
+M_PRECONDITIONER = np.array([[1.0, 0.1], [0.1, 0.5]])   # lmc.py:278, lmc_laplace.py:315, prox_lmc.py:374
+BETA_MIRROR = np.array([0.7, 0.3])                      # lmc.py:284, lmc_laplace.py:318, prox_lmc.py:380
+
+
+def mixture_parameters(n):
+    """Means / covariances of the drivers' n-component experiments (lmc.py:205-231, prox_lmc.py:274-300)."""
+    mu = [np.array(m) for m in ([0., 0.], [-2., 3.], [2., -3.], [3., 3.], [-2., -2.])]
+    Sg = [np.array(S) for S in ([[1., -0.5], [-0.5, 1.]], [[0.5, 0.2], [0.2, 0.7]], [[0.5, 0.1], [0.1, 0.9]],
+                                [[0.8, 0.02], [0.02, 0.3]], [[1.2, 0.05], [0.05, 0.8]])]
+    idx = {1: [0], 2: [0, 1], 3: [0, 1, 2], 4: [1, 2, 3, 4], 5: [0, 1, 2, 3, 4]}[n]
+    return [mu[i] for i in idx], [Sg[i] for i in idx], np.ones(n) / n
+
+
+def plot_grid(N=300, lo=-5.0, hi=5.0):
+    """The (N,N,2) evaluation grid of the drivers (lmc.py:198-201, 238-240)."""
+    X, Y = np.meshgrid(np.linspace(lo, hi, N), np.linspace(lo, hi, N))
+    return X, Y, np.stack([X, Y], axis=-1)
+
+
+def lmc_gaussian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamma_ihpula=5e-2, gamma_mla=5e-2, n=5,
+                         K=5000, seed=0, dtype="float64"):
+    """Headless ``lmc_gaussian_mixture`` (lmc.py:194-196; same keyword arguments = the CLI flags): runs the five
+    samplers on the CUDA path and returns what the reference goes on to plot.  Plotting, KDE and the POT
+    Wasserstein curves are outside the hot path; ``true_samples`` is returned for them."""
+    mus, Sigmas, omegas = mixture_parameters(n)
+    X, Y, pos = plot_grid()
+    lmc = LangevinMonteCarlo(mus, Sigmas, omegas, K, seed, dtype=dtype)
+    out = {"X": X, "Y": Y, "density": lmc.density_gaussian_mixture(pos), "true_samples": lmc.true_samples()}
+    out["ula"] = lmc.ula(gamma_ula)
+    out["mala"], out["mala_effective"] = lmc.mala(gamma_mala)
+    out["pula"] = lmc.pula(gamma_pula, M_PRECONDITIONER)
+    out["ihpula"] = lmc.ihpula(gamma_ihpula)
+    out["mla"] = lmc.mla(gamma_mla, BETA_MIRROR)
+    return out

@@ -4,6 +4,7 @@ from __future__ import annotations
 import numpy as np
 
 from . import _lib
+from .lmc import BETA_MIRROR, M_PRECONDITIONER, mixture_parameters, plot_grid
 from .mixtures import MixtureSampler
 
 
@@ -55,3 +56,47 @@ class LangevinMonteCarloLaplacian(MixtureSampler):
 
     def mla(self, gamma, beta):
         return self._reference_call("mla", gamma, beta=beta)
+
+    # ---- evaluation helpers of the driver (plot grids; host numpy, not on the sampler path) -----------
+    def multivariate_laplacian(self, theta, mu, alpha):
+        """(alpha/2)^d exp(-alpha |theta - mu|_1)   (lmc_laplace.py:43-44)."""
+        return (alpha / 2) ** self.d * np.exp(-alpha * np.abs(np.asarray(theta, dtype=np.float64) - mu).sum(axis=-1))
+
+    def density_laplacian_mixture(self, theta):
+        """lmc_laplace.py:46-48."""
+        return sum(self.omegas[i] * self.multivariate_laplacian(theta, self.mus[i], self.alphas[i])
+                   for i in range(len(self.alphas)))
+
+    def prox_uncentered_laplace(self, theta, gamma, mu):
+        """mu + soft(theta - mu, gamma)   (lmc_laplace.py:53-54, prox.py:18-19)."""
+        d = np.asarray(theta, dtype=np.float64) - mu
+        return mu + np.sign(d) * np.maximum(np.abs(d) - gamma, 0)
+
+    def moreau_env_uncentered_laplace(self, theta, mu, alpha):
+        """lmc_laplace.py:56-58."""
+        p = self.prox_uncentered_laplace(theta, self.lamda * alpha, mu)
+        return alpha * np.abs(p - mu).sum(axis=-1) + ((p - theta) ** 2).sum(axis=-1) / (2 * self.lamda)
+
+    def smooth_multivariate_laplacian(self, theta, mu, alpha):
+        return (alpha / 2) ** self.d * np.exp(-self.moreau_env_uncentered_laplace(theta, mu, alpha))
+
+    def smooth_density_laplacian_mixture(self, theta):
+        """lmc_laplace.py:63-65."""
+        return sum(self.omegas[i] * self.smooth_multivariate_laplacian(theta, self.mus[i], self.alphas[i])
+                   for i in range(len(self.alphas)))
+
+
+def lmc_laplacian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamma_mla=5e-2, lamda=1e-1, alpha=1e-1,
+                          n=5, K=5000, seed=0, dtype="float64"):
+    """Headless ``lmc_laplacian_mixture`` (lmc_laplace.py:220-222, same keyword arguments): ULA, MALA, PULA and
+    MLA on the smoothed Laplacian mixture through the CUDA path; returns the arrays the reference plots."""
+    mus, _, omegas = mixture_parameters(n)
+    X, Y, pos = plot_grid()
+    s = LangevinMonteCarloLaplacian(mus, np.ones(n) * alpha, omegas, lamda, K, seed, dtype=dtype)
+    out = {"X": X, "Y": Y, "density": s.density_laplacian_mixture(pos),
+           "smooth_density": s.smooth_density_laplacian_mixture(pos)}
+    out["ula"] = s.ula(gamma_ula)
+    out["mala"], out["mala_effective"] = s.mala(gamma_mala)
+    out["pula"] = s.pula(gamma_pula, M_PRECONDITIONER)
+    out["mla"] = s.mla(gamma_mla, BETA_MIRROR)
+    return out

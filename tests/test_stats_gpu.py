@@ -91,3 +91,52 @@ def test_fp32_production_posterior_mean_psnr_within_tolerance():
     got = algs.MoreauYosidaUnadjustedLangevin(l2, compat.TV(dims, sigma=0.3, niter=10), pb["x0"], tau=pb["tau_myula"],
                                               gamma=pb["gamma_myula"], niter=N, seed=0, dtype="float32")
     assert abs(D.psnr(xtrue, got.mean(axis=0)) - D.psnr(xtrue, want.mean(axis=0))) < 0.05
+
+
+@pytest.mark.parametrize("alg", ["ULPDA", "MYULA"])
+def test_headless_deconv_main_matches_oracle(alg):
+    """prox_lmc_deconv(...) with the driver's keywords on a small image: posterior means and PSNR of three of
+    the nine models (L2/H5, MC-TV/H6, ME-TV/H7) against the oracle's run of the same experiment."""
+    from oracle import deconv_ref as D
+    from lmc_atomi_b200.prox_lmc_deconv import prox_lmc_deconv
+    img = D.synthetic_image(40, 36).astype(np.float64)
+    N, models = 5, ((5, "l2"), (6, "mc"), (7, "me"))
+    out = prox_lmc_deconv(N=N, image=img, alg=alg, seed=0, models=models)
+    assert set(out["models"]) == {"l2_5", "mc_6", "me_7"}
+    for k, term in models:
+        pb = D.build_problem(img, kernel=k)
+        assert np.abs(out["observation"] - pb["y"]).max() < 1e-12
+        f = pb["l2"]() if term == "l2" else pb["l2_" + term]()
+        if alg == "ULPDA":
+            g = pb["l1"]() if term == "mc" else pb["l1iso"]()
+            want = D.UnadjustedLangevinPrimalDual(f, g, pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], theta=1.,
+                                                  niter=N, seed=0, gfirst=False)
+        else:
+            want = D.MoreauYosidaUnadjustedLangevin(f, pb["tv"](), pb["x0"], tau=pb["tau_myula"],
+                                                    gamma=pb["gamma_myula"], niter=N, seed=0)
+        m = out["models"][f"{term}_{k}"]
+        assert np.abs(m["mean"].ravel() - want.mean(axis=0)).max() <= 1e-8 * np.abs(want).max()
+        assert abs(m["mean_psnr"] - D.psnr(img.ravel(), want.mean(axis=0))) < 0.05
+        assert len(m["psnr"]) == N and abs(m["psnr"][-1] - D.psnr(img.ravel(), want[-1])) < 1e-6
+
+
+def test_headless_mixture_mains_reproduce_golden_chains():
+    from helpers import load_golden
+    from lmc_atomi_b200.lmc import lmc_gaussian_mixture
+    from lmc_atomi_b200.lmc_laplace import lmc_laplacian_mixture
+    from lmc_atomi_b200.prox_lmc import prox_lmc_gaussian_mixture
+    K = 300
+    g = load_golden("mix_gauss.npz")
+    out = lmc_gaussian_mixture(0.1, 0.1, 0.1, 0.1, 0.1, n=5, K=K, seed=0)
+    for a in ("ula", "pula", "ihpula", "mla"):
+        assert np.abs(out[a] - g[a][:K]).max() < 1e-11
+    assert out["density"].shape == (300, 300) and out["true_samples"].shape == (K, 2)
+    l = load_golden("mix_laplace.npz")
+    out = lmc_laplacian_mixture(0.05, 0.05, 0.05, 0.05, lamda=0.1, alpha=0.5, n=5, K=K, seed=0)
+    for a in ("ula", "pula", "mla"):
+        assert np.abs(out[a] - l[a][:K]).max() < 1e-11
+    assert out["mala"].shape == (out["mala_effective"], 2)
+    p = load_golden("mix_prox.npz")
+    out = prox_lmc_gaussian_mixture(0.05, 0.05, 0.05, 0.05, 0.05, 0.05, lamda=0.25, alpha=0.15, n=5, t=100, K=K, seed=0)
+    for a in ("pgld", "myula", "ppula", "fbula", "lbmumla"):
+        assert np.abs(out[a] - p[a][:K]).max() < 1e-10
