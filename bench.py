@@ -235,6 +235,8 @@ def run_ours(args):
     h2d = C * 2 * 4 * len(ALGS)
     d2h = (C * 2 * 4 + 6 * 8 + 100 * 100 * 8 + 4 * 0) * len(ALGS) + C * 4  # + MALA accept counts
 
+    # image half of the metric (configs 3-4): every rank advances its own shard of the image chains
+    extra = image_bench(args, dev) if not args.no_image else None
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -270,7 +272,6 @@ def run_ours(args):
     if cpu is not None:
         line["cpu_baseline"] = {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
                                 "sample": cpu["sample"], "per_core": cpu["per_core"]}
-    extra = image_bench(args, dev) if (world == 1 and not args.no_image) else None
     if extra is not None:
         line["myula_deconv"] = extra
     print(json.dumps(line), flush=True)

@@ -43,17 +43,70 @@ def make_engine(dims, dev, dtype="float32", kernel=5, seed=0):
     return img, imaging.DeconvEngine(dims, hk, y, 1.0 / SIGMA ** 2, dtype=dtype, device=dev)
 
 
+def _world():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return dist, dist.get_world_size(), dist.get_rank()
+    return None, 1, 0
+
+
 def _time_launches(torch, dev, fn, steps, warmup):
+    """Seconds per launch, CUDA events on the launching stream, barrier + synchronize on both sides, MAX over
+    the ranks when a process group is up (each rank advances its own shard of the chains)."""
+    dist, world, _ = _world()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
     for _ in range(warmup):
         fn()
-    torch.cuda.synchronize(dev)
+    barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(steps):
         fn()
     b.record()
+    barrier()
+    t = torch.tensor([a.elapsed_time(b) * 1e-3 / steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _e2e(torch, dev, x, mean, launch, units, reps=2):
+    """The same metric through host buffers: per repetition the start states come from pinned host memory and
+    the posterior mean goes back to it, both inside the timed region (MAX over ranks)."""
+    dist, world, _ = _world()
+    h_x = torch.zeros(x.shape, dtype=x.dtype).pin_memory()
+    h_mean = torch.empty(mean.shape, dtype=mean.dtype).pin_memory()
+    if world > 1:
+        dist.barrier()
     torch.cuda.synchronize(dev)
-    return a.elapsed_time(b) * 1e-3 / steps
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        x.copy_(h_x, non_blocking=True)
+        launch()
+        h_mean.copy_(mean, non_blocking=True)
+    b.record()
+    torch.cuda.synchronize(dev)
+    t = torch.tensor([a.elapsed_time(b) * 1e-3 / reps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    nbytes = x.numel() * x.element_size()
+    return {"value": world * units / float(t.item()), "unit": "chain-iters/s", "h2d_bytes_per_step": nbytes,
+            "d2h_bytes_per_step": nbytes}
+
+
+def _pooled_mean(torch, mean):
+    """The only collective of the image path: posterior mean pooled over all chains of all ranks."""
+    dist, world, _ = _world()
+    s = mean.double().sum(dim=0)
+    if world > 1:
+        dist.all_reduce(s)
+    return s / (mean.shape[0] * world)
 
 
 # measured once per round with `ncu --set full` (profiles/): dram__bytes_read+write per launch of the
@@ -70,10 +123,11 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     x = torch.zeros((chains, P), dtype=eng.tdt, device=dev)
     mean = torch.zeros_like(x)
     state = {"it": 0, "keep": None}
+    _, world, rank = _world()
 
     def launch():
         state["keep"] = eng.myula(x, iters, tau, gamma, TAU_REG, 10, 1e-4, seed=0, mean=mean,
-                                  iter_offset=state["it"], engine=engine)
+                                  iter_offset=state["it"], engine=engine, chain_offset=rank * chains)
         state["it"] += iters
 
     for _ in range(2):      # burn-in so that the TV early exit is in its steady regime
@@ -83,7 +137,9 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     it0 = state["it"]
     secs = _time_launches(torch, dev, launch, steps, warmup)
     c = eng.read_counters()
-    n_it = state["it"] - it0
+    pooled = _pooled_mean(torch, mean)
+    e2e = _e2e(torch, dev, x, mean, launch, chains * iters)
+    n_it = state["it"] - it0 - 2 * iters
     j = c["tv_sweeps"] / float(n_it * chains)
     item = 4 if dtype == "float32" else 8
     bpp = roofline.myula_bytes_per_pixel(j, item)
@@ -102,10 +158,12 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     else:
         kernel = "img_myula_kernel<%s>" % ("float" if item == 4 else "double")
         policy, traffic, note = "per-chain arrays total far more than the 126 MB L2", None, None
-    out = {"metric": "myula_deconv_chain_iters_per_sec", "value": chains * iters / secs, "unit": "chain-iters/s",
-           "pixel_iters_per_sec": chains * iters * P / secs, "dtype": dtype, "dims": list(dims), "chains": chains,
+    out = {"metric": "myula_deconv_chain_iters_per_sec", "value": world * chains * iters / secs,
+           "unit": "chain-iters/s", "n_gpus": world, "pooled_mean_finite": bool(torch.isfinite(pooled).all().item()),
+           "pixel_iters_per_sec": world * chains * iters * P / secs, "dtype": dtype, "dims": list(dims),
+           "chains": chains,
            "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "tv_sweeps_per_iter": j,
-           "engine": "onchip" if onchip else "stream", "state_bytes": int(10 * chains * P * item), "l2_policy": policy,
+           "e2e": e2e, "engine": "onchip" if onchip else "stream", "state_bytes": int(10 * chains * P * item), "l2_policy": policy,
            "roofline": {"bound": "hbm", "kernel": kernel,
                         "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
                         "bytes_per_pixel_iter": bpp, "traffic": traffic, "peak_source": peaks["source"]}}
@@ -123,11 +181,12 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
     z = lambda *s: torch.zeros(s, dtype=eng.tdt, device=dev)
     x, xhat, y, warm, mean = z(chains, P), z(chains, P), z(chains, 2, P), z(chains, P), z(chains, P)
     state = {"it": 0, "keep": None}
+    _, world, rank = _world()
 
     def launch():
         state["keep"] = eng.ulpda(x, xhat, y, warm, iters, tau, mu, 1.0, TAU_REG, True, False, 50, seed=0,
                                   mean=mean, iter_offset=state["it"], engine=engine,
-                                  group=group)
+                                  group=group, chain_offset=rank * chains)
         state["it"] += iters
 
     for _ in range(3):
@@ -136,14 +195,18 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
     eng.counters.zero_()
     secs = _time_launches(torch, dev, launch, steps, warmup)
     c = eng.read_counters()
+    pooled = _pooled_mean(torch, mean)
+    e2e = _e2e(torch, dev, x, mean, launch, chains * iters)
     k = c["lsqr_iterations"] / max(1.0, float(c["lsqr_solves"]))
     item = 4 if dtype == "float32" else 8
     bpp = roofline.ulpda_bytes_per_pixel(k, item)
     peaks = roofline.measured_peaks()
     ach = bpp * P * chains * iters / secs / 1e9
-    return {"metric": "ulpda_deconv_chain_iters_per_sec", "value": chains * iters / secs, "unit": "chain-iters/s",
-            "pixel_iters_per_sec": chains * iters * P / secs, "dtype": dtype, "dims": list(dims), "chains": chains,
-            "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "lsqr_iters_per_solve": k,
+    return {"metric": "ulpda_deconv_chain_iters_per_sec", "value": world * chains * iters / secs,
+            "unit": "chain-iters/s", "n_gpus": world, "pooled_mean_finite": bool(torch.isfinite(pooled).all().item()),
+            "pixel_iters_per_sec": world * chains * iters * P / secs, "dtype": dtype, "dims": list(dims),
+            "chains": chains,
+            "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "lsqr_iters_per_solve": k, "e2e": e2e,
             "engine": "band" if (engine == "band" or (engine == "auto" and eng.band_supported())) else "tile",
             "group": group,
             "roofline": {"bound": "hbm", "kernel": ("img_ulpda_band_kernel<%s,5,16>" if (
