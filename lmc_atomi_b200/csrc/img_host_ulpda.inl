@@ -27,7 +27,6 @@ bool band_supported(const lmc_img_problem* pb) {
 template <typename real>
 bool band_pairs(const UlpdaArgs<real>& A) {
   if (A.g.ntap_x != 5 || A.g.lo_x != -2 || (A.g.nx & 1)) return false;
-  if (getenv("LMC_BAND_SCALAR") != nullptr) return false;   // experiments: one column per thread
   const void* ptrs[] = {A.x, A.y, A.warm, A.optb, A.u, A.v, A.w, A.in, A.b};
   for (const void* p : ptrs)
     if (reinterpret_cast<size_t>(p) % (2 * sizeof(real)) != 0) return false;
