@@ -81,6 +81,35 @@ def cpu_sample(k_unadj=3000, k_adj=800, cores=None):
             "sample": f"{cores} chains (1 per core) x ({k_unadj} steps ULA/PULA/MLA + {k_adj} steps MALA), numpy float64"}
 
 
+def _cpu_image_worker(args):
+    """One host core: the oracle port of the image samplers (numpy + scipy FFT convolution + scipy LSQR,
+    oracle/deconv_ref.py restating algs.py:295-587) on one chain."""
+    which, seed, dims, iters = args
+    from oracle import deconv_ref as D
+    pb = D.build_problem(D.synthetic_image(*dims), seed=0)
+    t0 = time.perf_counter()
+    if which == "myula":
+        D.MoreauYosidaUnadjustedLangevin(pb["l2"](), pb["tv"](), pb["x0"], tau=pb["tau_myula"], gamma=pb["gamma_myula"],
+                                         niter=iters, seed=seed)
+    else:
+        D.UnadjustedLangevinPrimalDual(pb["l2"](), pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], theta=1.,
+                                       niter=iters, seed=seed, gfirst=False)
+    return iters, time.perf_counter() - t0
+
+
+def cpu_image_sample(which, dims, iters, cores=None):
+    """chain-iters/s of the CPU port with one independent chain per host core."""
+    import multiprocessing as mp
+    cores = cores or os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    with mp.get_context("fork").Pool(cores) as pool:
+        res = pool.map(_cpu_image_worker, [(which, s, dims, iters) for s in range(cores)])
+    per_core = float(np.mean([n / t for n, t in res]))
+    return {"value": per_core * cores, "unit": "chain-iters/s", "cores": cores, "kind": "port", "per_core": per_core,
+            "sample": f"{cores} chains (1 per core) x {iters} iterations of {dims[0]}x{dims[1]} {which.upper()}, "
+                      "numpy float64 + scipy FFT convolution" + (" + scipy LSQR" if which == "ulpda" else "")}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -257,7 +286,9 @@ def run_ours(args):
     ach = roofline.mix_laneops_per_step("laplace", dom) * C * K / secs
     roof = {"bound": "fp32-issue", "kernel": f"mix_chain_kernel<float,LAPLACE,{dom.upper()},5>",
             "achieved": ach / 1e12, "peak": peak_ops / 1e12, "unit": "Tlane-op/s", "frac": ach / peak_ops,
-            "traffic": None, "peak_source": f"148 SMs x 128 lanes x {sm_mhz_peak:.0f} MHz ({peaks['source']} sm_max_mhz)",
+            "traffic": roofline.MIX_DRAM_BYTES_PER_LAUNCH.get(dom),
+            "issue_active_pct_ncu": roofline.MIX_ISSUE_ACTIVE_PCT.get(dom),
+            "peak_source": f"148 SMs x 128 lanes x {sm_mhz_peak:.0f} MHz ({peaks['source']} sm_max_mhz)",
             "note": "register-resident chains: no HBM traffic in steady state, so the bound is FP32/INT32 issue "
                     "(north_star); algorithmic lane-ops per step from lmc_atomi_b200/roofline.py",
             "per_sampler": per_alg}
@@ -273,6 +304,9 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
                                 "sample": cpu["sample"], "per_core": cpu["per_core"]}
     if extra is not None:
+        if cpu is not None:   # the CPU port of the image samplers, timed beside them (bounded sample)
+            extra["cpu_baseline"] = cpu_image_sample("myula", tuple(extra["dims"]), 8)
+            extra["ulpda"]["cpu_baseline"] = cpu_image_sample("ulpda", tuple(extra["ulpda"]["dims"]), 2)
         line["myula_deconv"] = extra
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -202,6 +202,7 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
     bpp = roofline.ulpda_bytes_per_pixel(k, item)
     peaks = roofline.measured_peaks()
     ach = bpp * P * chains * iters / secs / 1e9
+    band = engine == "band" or (engine == "auto" and eng.band_supported())
     return {"metric": "ulpda_deconv_chain_iters_per_sec", "value": world * chains * iters / secs,
             "unit": "chain-iters/s", "n_gpus": world, "pooled_mean_finite": bool(torch.isfinite(pooled).all().item()),
             "pixel_iters_per_sec": world * chains * iters * P / secs, "dtype": dtype, "dims": list(dims),
@@ -213,7 +214,10 @@ def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtyp
                 engine == "band" or (engine == "auto" and eng.band_supported())) else "img_ulpda_kernel<%s>") % (
                 "float" if item == 4 else "double"),
                          "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
-                         "bytes_per_pixel_iter": bpp, "traffic": None, "peak_source": peaks["source"]}}
+                         "bytes_per_pixel_iter": bpp,
+                         "traffic": (roofline.ULPDA_BAND_DRAM_BYTES_PER_CHAIN_ITER * chains * iters
+                                     if (band and dims == (512, 512)) else None),
+                         "peak_source": peaks["source"]}}
 
 
 def run(dev, steps=3, warmup=3, **kw):

@@ -67,3 +67,11 @@ def myula_bytes_per_pixel(j_exec: float, itemsize: int = 4) -> float:
 def ulpda_bytes_per_pixel(k_exec: float, itemsize: int = 4) -> float:
     """(24 + 16 k) transfers."""
     return (24 + 16 * k_exec) * itemsize
+
+
+# ---- measured once per round with `ncu --set full` (profiles/r01e_*): dram__bytes_read.sum + dram__bytes_write.sum
+# per launch of the kernel, used for `roofline.traffic`.  Captures are of smaller launches than the bench's
+# (ncu replays every kernel ~40 times); the per-unit figures below are what scales.
+MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 125.2e3, "mala": 104.7e3, "pula": 126.5e3, "mla": 131.6e3}   # state is in registers
+MIX_ISSUE_ACTIVE_PCT = {"ula": 83.0, "mala": 78.3, "pula": 84.4, "mla": 78.3}       # smsp__issue_active, same capture
+ULPDA_BAND_DRAM_BYTES_PER_CHAIN_ITER = (34.459e9 + 23.259e9) / 512.0   # 512x512, H5, k = 8: 256 chains x 2 iterations
