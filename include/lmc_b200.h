@@ -206,6 +206,14 @@ int lmc_img_ulpda_run_band(const lmc_img_problem* pb, const lmc_img_ulpda_params
                            int64_t N, uint64_t seed, uint64_t chain_offset, int64_t group, const lmc_img_io* io,
                            void* stream);
 
+/* MYULA, row-band formulation (csrc/img_myula_band.inl): bands of 16 full-width rows, fused two-pass H^T H with
+ * compile-time taps, TV sweeps on 8-row sub-bands, two columns per thread, work items drawn from a global queue.
+ * Same arguments, workspace and results as lmc_img_myula_run; requires the 5 x 5 blur centred at (2, 2), an even
+ * width and buffers aligned to two elements (lmc_img_myula_band_supported() != 0). */
+int lmc_img_myula_band_supported(const lmc_img_problem* pb, int dtype);
+int lmc_img_myula_run_band(const lmc_img_problem* pb, const lmc_img_myula_params* pr, int dtype, int64_t C,
+                           int64_t N, uint64_t seed, uint64_t chain_offset, const lmc_img_io* io, void* stream);
+
 /* MYULA with the whole chain state ON CHIP (csrc/img_myula_onchip.cu): one thread-block
  * cluster of 8 CTAs per chain, x and the TV dual field in (distributed) shared memory for
  * all N iterations.  Same arguments, noise stream and results (to fp32 rounding) as

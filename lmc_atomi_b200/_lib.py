@@ -101,6 +101,9 @@ SIGNATURES = {
     "lmc_img_myula_run": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgMyulaParams), C.c_int, C.c_int64,
                                     C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),
     "lmc_img_myula_onchip_supported": (C.c_int, [C.POINTER(ImgProblem), C.c_int]),
+    "lmc_img_myula_band_supported": (C.c_int, [C.POINTER(ImgProblem), C.c_int]),
+    "lmc_img_myula_run_band": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgMyulaParams), C.c_int, C.c_int64,
+                                         C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),
     "lmc_img_myula_onchip_clusters": (C.c_int, []),
     "lmc_img_myula_run_onchip": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgMyulaParams), C.c_int, C.c_int64,
                                            C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),

@@ -6,23 +6,58 @@ namespace {
 template <typename real>
 size_t myula_ws_bytes(int ny, int nx, long long C) {
   const size_t P = (size_t)ny * nx;
-  const size_t tiles = (size_t)((ny + TH - 1) / TH) * ((nx + TW - 1) / TW);
+  size_t tiles = (size_t)((ny + TH - 1) / TH) * ((nx + TW - 1) / TW);
+  const size_t bands = (size_t)(ny + MB_RB - 1) / MB_RB;   // the band kernel keeps one partial per band
+  if (bands > tiles) tiles = bands;
   return 256 /* n_active + counters */ + align_up(C * sizeof(TvState)) + align_up(C * tiles * sizeof(double)) +
          align_up((size_t)C * P * sizeof(real)) /* grad */ + align_up((size_t)6 * C * P * sizeof(real)) /* duals */;
+}
+
+// the band kernel covers the H5 blur of the benchmark configurations with two columns per thread
+template <typename real>
+bool myula_band_ok(const lmc_img_problem* pb) {
+  if (pb->ntap_y != 5 || pb->ntap_x != 5 || pb->lo_x != -2 || (pb->nx & 1)) return false;
+  return myula_band_smem_bytes<real, 5>(band_pitch(pb->nx)) <= 200 * 1024;
+}
+
+template <typename real>
+int launch_myula_band(MyulaArgs<real>& A, cudaStream_t st) {
+  const size_t smem = myula_band_smem_bytes<real, 5>(A.pitch);
+  auto kern = img_myula_band_kernel<real, 5>;
+  int dev = 0, sms = 0, occ = 0;
+  LMC_CUDA_OK(cudaGetDevice(&dev));
+  LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  LMC_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  LMC_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, BAND_BT, smem));
+  LMC_REQUIRE(occ >= 1, "MYULA band kernel does not fit on an SM (smem %zu)", smem);
+  const long long cap = (long long)sms * occ, items = A.C * A.g.tiles;
+  LMC_REQUIRE(items < (1ll << 31) && A.g.P < (1ll << 31), "MYULA band kernel: 32-bit item / pixel indices exceeded");
+  int grid = (int)(items < cap ? items : cap);
+  if (grid < 1) grid = 1;
+  void* kargs[] = {(void*)&A};
+  LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(BAND_BT), kargs, smem, st));
+  return 0;
 }
 
 template <typename real>
 int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long long C, long long N, uint64_t seed,
               uint64_t chain_offset, const lmc_img_io* io, int mode, const void* tv_in, void* tv_out,
-              cudaStream_t st) {
+              cudaStream_t st, bool band = false) {
   MyulaArgs<real> A;
   memset(&A, 0, sizeof(A));
   fill_geom(pb, A.g);
+  if (band) {   // one objective partial per band of MB_RB rows
+    A.g.tiles_x = 1;
+    A.g.tiles_y = (pb->ny + MB_RB - 1) / MB_RB;
+    A.g.tiles = A.g.tiles_y;
+    A.pitch = band_pitch(pb->nx);
+  }
   const size_t need = myula_ws_bytes<real>(pb->ny, pb->nx, C);
   LMC_REQUIRE(io->d_workspace != nullptr && io->workspace_bytes >= need, "image workspace too small (%zu < %zu)",
               io->workspace_bytes, need);
   char* ws = (char*)io->d_workspace;
   A.n_active = (int*)ws;
+  A.queue = (int*)(ws + 128);
   unsigned long long* local_counters = (unsigned long long*)(ws + 64);
   ws += 256;
   A.st = (TvState*)ws;
@@ -65,6 +100,13 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
     A.tv_gamma = (real)pr->tv_sigma;   // caller passes gamma = sigma * tau here
   }
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
+  if (band) {
+    const void* ptrs[] = {A.x, A.b, A.grad, A.D};
+    for (const void* p : ptrs)
+      LMC_REQUIRE(reinterpret_cast<size_t>(p) % (2 * sizeof(real)) == 0,
+                  "MYULA band kernel: buffers must be aligned to two elements");
+    return launch_myula_band<real>(A, st);
+  }
   return launch_persistent(img_myula_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);
 }
 
@@ -93,6 +135,36 @@ extern "C" int lmc_img_myula_run(const lmc_img_problem* pb, const lmc_img_myula_
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64 ? run_myula<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st)
                           : run_myula<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st);
+}
+
+extern "C" int lmc_img_myula_band_supported(const lmc_img_problem* pb, int dtype) {
+  if (pb == nullptr || pb->ny < 1 || pb->nx < 1) return 0;
+  if (dtype == LMC_F32) return myula_band_ok<float>(pb) ? 1 : 0;
+  if (dtype == LMC_F64) return myula_band_ok<double>(pb) ? 1 : 0;
+  return 0;
+}
+
+extern "C" int lmc_img_myula_run_band(const lmc_img_problem* pb, const lmc_img_myula_params* pr, int dtype, int64_t C,
+                                 int64_t N, uint64_t seed, uint64_t chain_offset, const lmc_img_io* io,
+                                 void* stream) {
+  if (check_problem(pb, "lmc_img_myula_run_band") != 0) return -1;
+  LMC_REQUIRE(pr != nullptr && io != nullptr, "lmc_img_myula_run_band: null descriptor");
+  LMC_REQUIRE(dtype == LMC_F32 || dtype == LMC_F64, "lmc_img_myula_run_band: dtype must be LMC_F32 or LMC_F64");
+  LMC_REQUIRE(C >= 0 && N >= 0, "lmc_img_myula_run_band: negative C or N");
+  LMC_REQUIRE(pr->tau > 0 && pr->gamma > 0, "lmc_img_myula_run_band: tau and gamma must be positive");
+  LMC_REQUIRE(pr->tv_niter >= 0 && pr->tv_sigma * pr->epsg * pr->gamma > 0,
+              "lmc_img_myula_run_band: TV needs niter >= 0 and sigma*epsg*gamma > 0");
+  LMC_REQUIRE(lmc_img_myula_band_supported(pb, dtype),
+              "lmc_img_myula_run_band: needs the 5 x 5 blur centred at (2, 2), an even width and a row that fits in "
+              "shared memory (use lmc_img_myula_run)");
+  if (C == 0 || N == 0) return 0;
+  LMC_REQUIRE(io->d_x != nullptr && pb->d_b != nullptr, "lmc_img_myula_run_band: d_x and d_b are required");
+  LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
+              "lmc_img_myula_run_band: b_chain_stride must be 0 or ny*nx");
+  LMC_REQUIRE(io->d_fgrad_extra == nullptr || N == 1, "lmc_img_myula_run_band: d_fgrad_extra needs N == 1");
+  cudaStream_t st = (cudaStream_t)stream;
+  return dtype == LMC_F64 ? run_myula<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true)
+                          : run_myula<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true);
 }
 
 extern "C" int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, int32_t niter, double rtol,

@@ -52,6 +52,9 @@ struct MyulaArgs {
   int tv_niter;
   double tv_rtol;
   int mode;  // 0 = MYULA, 1 = TV prox only (out = prox_{tv_gamma TV}(x))
+  // band kernel only (img_myula_band.inl)
+  int pitch;        // shared-memory row pitch in elements
+  int* queue;       // 4 work-queue counters (BandSched)
 };
 
 __device__ __forceinline__ double fista_c(int it) {
@@ -331,4 +334,5 @@ __global__ void __launch_bounds__(NTHREADS) img_myula_kernel(const __grid_consta
 
 }  // namespace
 
+#include "img_myula_band.inl"
 #include "img_host.inl"

@@ -1,0 +1,294 @@
+// MYULA, row-band formulation (included by img_myula.cu; same arguments, TV state machine and scalar phase as
+// the tile kernel above, different data movement -- the general path for images that do not fit the on-chip
+// cluster kernel, e.g. the reference's 512 x 512 camera image, and for fp64).
+//
+//   G   : a band of 16 rows + blur halo staged once; g = sigma H^T mask(Hx - b) by the two fused separable
+//         passes of img_band.cuh; TV sweep 0 (sol_0 = x) runs in the epilogue out of the staged x
+//   T_k : sub-bands of 8 rows: rr, ss = p_k + c_k (p_k - p_{k-1}) staged with one halo row, sol_k on 9 rows into
+//         shared memory, then the projected dual update and the objective of the pixel
+//   U   : sol_kf recomputed from the staged (rr, ss), the MYULA update, running statistics
+// Two image columns per thread (8/16-byte vectors); work items drawn from the BandSched queue.
+#include "img_band.cuh"
+
+namespace {
+
+constexpr int MB_RB = 16;   // rows per band = per objective partial
+constexpr int MB_HB = 8;    // rows per TV sub-band
+constexpr int MB_W = 2;     // image columns per thread
+
+template <typename real, int NT>
+__host__ __device__ inline size_t myula_band_smem_bytes(int pitch) {
+  const int a = Band<real, NT, MB_RB>::XROWS + Band<real, NT, MB_RB>::TROWS, b = 3 * (MB_HB + 2);
+  return (size_t)(a > b ? a : b) * pitch * sizeof(real);
+}
+
+// rr = p_it + c (p_it - p_{it-1}) (both components) on image rows [r_first, r_first + nrows), all columns;
+// zero outside the image (pad columns are never written and stay zero)
+template <typename real>
+__device__ __forceinline__ void mband_stage_rr(const MyulaArgs<real>& A, long long chain, int it, int r_first, int nrows,
+                                               real* RR, real* SS) {
+  using P2 = Pack<real, MB_W>;
+  const Geom<real>& g = A.g;
+  const int pitch = A.pitch;
+  const real c = (real)fista_c(it);
+  const real* pa = dual_ptr(A, it % 3, 0, chain);
+  const real* qa = dual_ptr(A, it % 3, 1, chain);
+  const real* pb = dual_ptr(A, (it + 2) % 3, 0, chain);
+  const real* qb = dual_ptr(A, (it + 2) % 3, 1, chain);
+  for (int col = MB_W * threadIdx.x; col < g.nx; col += MB_W * BAND_BT) {
+#pragma unroll 5
+    for (int a = 0; a < nrows; ++a) {
+      const int i = r_first + a;
+      P2 r, s;
+#pragma unroll
+      for (int q = 0; q < MB_W; ++q) r.a[q] = s.a[q] = real(0);
+      if (it >= 1 && i >= 0 && i < g.ny) {
+        const int o = i * g.nx + col;
+        const P2 p = ldp<real, MB_W>(pa + o), q2 = ldp<real, MB_W>(qa + o);
+        if (it >= 2) {
+          const P2 pp = ldp<real, MB_W>(pb + o), qq = ldp<real, MB_W>(qb + o);
+#pragma unroll
+          for (int q = 0; q < MB_W; ++q) {
+            r.a[q] = p.a[q] + c * (p.a[q] - pp.a[q]);
+            s.a[q] = q2.a[q] + c * (q2.a[q] - qq.a[q]);
+          }
+        } else {   // c_1 = 0 and p_0 = 0
+          r = p;
+          s = q2;
+        }
+      }
+      stp<real, MB_W>(RR + a * pitch + BAND_PAD + col, r);
+      stp<real, MB_W>(SS + a * pitch + BAND_PAD + col, s);
+    }
+  }
+}
+
+// sol = x - gamma div(rr, ss) for columns [col, col + W) of local row a (RR/SS row a = image row, row a-1 above)
+template <typename real>
+__device__ __forceinline__ Pack<real, MB_W> mband_sol(const real* RR, const real* SS, int pitch, int a, int col,
+                                                      const Pack<real, MB_W>& xv, real gamma) {
+  using P2 = Pack<real, MB_W>;
+  const P2 rc = ldp<real, MB_W>(RR + a * pitch + BAND_PAD + col), ru = ldp<real, MB_W>(RR + (a - 1) * pitch + BAND_PAD + col);
+  const P2 sc = ldp<real, MB_W>(SS + a * pitch + BAND_PAD + col);
+  const real sl = SS[a * pitch + BAND_PAD + col - 1];
+  P2 out;
+#pragma unroll
+  for (int q = 0; q < MB_W; ++q) {
+    const real t = ((-rc.a[q] + ru.a[q]) - sc.a[q]) + (q == 0 ? sl : sc.a[q > 0 ? q - 1 : 0]);   // order of sol_at()
+    out.a[q] = xv.a[q] - gamma * (-t);
+  }
+  return out;
+}
+
+// ---------------------------------------------------------------- phase G (+ sweep 0)
+template <typename real, int NT>
+__device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, real* smem, double* red) {
+  using P2 = Pack<real, MB_W>;
+  constexpr int RB = MB_RB, E = NT - 1;
+  const Geom<real>& g = A.g;
+  const int pitch = A.pitch, items = (int)A.C * g.tiles;
+  real* X = smem;
+  real* T = smem + Band<real, NT, RB>::XROWS * pitch;
+  const real* wx = A.g.wx;
+  const real* wy = A.g.wy;
+  const real g8 = real(8) * A.tv_gamma;
+  sched.begin();
+  for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
+    long long chain; int i0;
+    band_of(g, w, 0, RB, chain, i0);
+    const real* bc = A.b + chain * A.b_stride;
+    real* gout = A.grad + chain * g.P;
+    real* p1 = dual_ptr(A, 1, 0, chain);
+    real* q1 = dual_ptr(A, 1, 1, chain);
+    band_stage(X, pitch, A.x + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
+    band_forward<real, NT, RB, MB_W>(g, X, T, pitch, i0, wx, wy,
+                                     [&](int i, int c) { return ldp<real, MB_W>(bc + i * g.nx + c); });
+    __syncthreads();
+    double acc = 0, none = 0;
+    BandPf<real, MB_W, 0, 4> pf;
+    band_adjoint<real, NT, RB, MB_W, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, P2 (&)[1]) {},
+                                           [&](int i, int c, int k, const P2& gv, const P2 (&)[1]) {
+      const int o = i * g.nx + c;
+      P2 go;
+#pragma unroll
+      for (int q = 0; q < MB_W; ++q) go.a[q] = A.sigma_l2 * gv.a[q];
+      stp<real, MB_W>(gout + o, go);
+      // TV sweep 0: rr = ss = 0 -> sol = x, obj = gamma sum |grad x|, p_1 = proj(-grad x / (8 gamma))
+      const real* xr = X + (k + E) * pitch + BAND_PAD + c;
+      const P2 xv = ldp<real, MB_W>(xr), xd = ldp<real, MB_W>(xr + pitch);
+      const real xright = xr[MB_W];
+      P2 pn, qn;
+#pragma unroll
+      for (int q = 0; q < MB_W; ++q) {
+        const real dx = (i < g.ny - 1) ? xd.a[q] - xv.a[q] : real(0);
+        const real dy = (c + q < g.nx - 1) ? (q + 1 < MB_W ? xv.a[q + 1 < MB_W ? q + 1 : 0] : xright) - xv.a[q] : real(0);
+        acc += (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
+        dual_update(real(0), real(0), dx, dy, g8, pn.a[q], qn.a[q]);
+      }
+      stp<real, MB_W>(p1 + o, pn);
+      stp<real, MB_W>(q1 + o, qn);
+    });
+    band_block_sum2(acc, none, red);
+    if (threadIdx.x == 0) A.partial[chain * g.tiles + i0 / RB] = acc;
+  }
+}
+
+// ---------------------------------------------------------------- phase T_it
+template <typename real>
+__device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int it, real* smem, double* red) {
+  using P2 = Pack<real, MB_W>;
+  constexpr int RB = MB_RB, HB = MB_HB;
+  const Geom<real>& g = A.g;
+  const int pitch = A.pitch, items = (int)A.C * g.tiles;
+  real* RR = smem;                        // local row a <-> image row r0 - 1 + a, a = 0 .. HB + 1
+  real* SS = RR + (HB + 2) * pitch;
+  real* SOL = SS + (HB + 2) * pitch;      // local row a <-> image row r0 + a, a = 0 .. HB
+  const real g8 = real(8) * A.tv_gamma;
+  sched.begin();
+  for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
+    long long chain; int i0;
+    band_of(g, w, 0, RB, chain, i0);
+    if (!A.st[chain].active) continue;
+    const real* xc = A.x + chain * g.P;
+    real* pn = dual_ptr(A, (it + 1) % 3, 0, chain);
+    real* qn = dual_ptr(A, (it + 1) % 3, 1, chain);
+    double acc = 0, none = 0;
+    for (int r0 = i0; r0 < i0 + RB && r0 < g.ny; r0 += HB) {
+      if (r0 != i0) __syncthreads();   // the previous sub-band's readers are done
+      mband_stage_rr(A, chain, it, r0 - 1, HB + 2, RR, SS);
+      __syncthreads();
+      for (int col = MB_W * threadIdx.x; col < g.nx; col += MB_W * BAND_BT) {
+#pragma unroll 3
+        for (int a = 0; a <= HB; ++a) {
+          const int i = r0 + a;
+          P2 xv;
+#pragma unroll
+          for (int q = 0; q < MB_W; ++q) xv.a[q] = real(0);
+          if (i < g.ny) xv = ldp<real, MB_W>(xc + i * g.nx + col);
+          stp<real, MB_W>(SOL + a * pitch + BAND_PAD + col, mband_sol(RR, SS, pitch, a + 1, col, xv, A.tv_gamma));
+        }
+      }
+      __syncthreads();
+      for (int col = MB_W * threadIdx.x; col < g.nx; col += MB_W * BAND_BT) {
+#pragma unroll 2
+        for (int a = 0; a < HB; ++a) {
+          const int i = r0 + a;
+          if (i >= g.ny) break;
+          const int o = i * g.nx + col;
+          const real* sr = SOL + a * pitch + BAND_PAD + col;
+          const P2 sv = ldp<real, MB_W>(sr), sd = ldp<real, MB_W>(sr + pitch), xv = ldp<real, MB_W>(xc + o);
+          const real sright = sr[MB_W];
+          const P2 rc = ldp<real, MB_W>(RR + (a + 1) * pitch + BAND_PAD + col),
+                   sc = ldp<real, MB_W>(SS + (a + 1) * pitch + BAND_PAD + col);
+          P2 po, qo;
+#pragma unroll
+          for (int q = 0; q < MB_W; ++q) {
+            const real dx = (i < g.ny - 1) ? sd.a[q] - sv.a[q] : real(0);
+            const real dy = (col + q < g.nx - 1) ? (q + 1 < MB_W ? sv.a[q + 1 < MB_W ? q + 1 : 0] : sright) - sv.a[q] : real(0);
+            const real df = xv.a[q] - sv.a[q];
+            acc += 0.5 * (double)df * (double)df + (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
+            dual_update(rc.a[q], sc.a[q], dx, dy, g8, po.a[q], qo.a[q]);
+          }
+          stp<real, MB_W>(pn + o, po);
+          stp<real, MB_W>(qn + o, qo);
+        }
+      }
+    }
+    band_block_sum2(acc, none, red);
+    if (threadIdx.x == 0) A.partial[chain * g.tiles + i0 / RB] = acc;
+  }
+}
+
+// ---------------------------------------------------------------- phase U
+template <typename real>
+__device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long long n, real* smem) {
+  constexpr int RB = MB_RB, HB = MB_HB;
+  const Geom<real>& g = A.g;
+  const int pitch = A.pitch, items = (int)A.C * g.tiles;
+  real* RR = smem;                        // local row a <-> image row r0 - 1 + a, a = 0 .. HB
+  real* SS = RR + (HB + 2) * pitch;
+  const int quads_per_row = (g.nx + 3) / 4;
+  const unsigned long long it_global = A.iter_offset + (unsigned long long)n;
+  const bool stats = (A.mean != nullptr) && ((long long)it_global >= A.burnin);
+  const real cntn = (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
+  sched.begin();
+  for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
+    long long chain; int i0;
+    band_of(g, w, 0, RB, chain, i0);
+    const int kf = A.st[chain].kf;
+    real* xc = A.x + chain * g.P;
+    for (int r0 = i0; r0 < i0 + RB && r0 < g.ny; r0 += HB) {
+      if (r0 != i0) __syncthreads();
+      mband_stage_rr(A, chain, kf, r0 - 1, HB + 1, RR, SS);
+      __syncthreads();
+      // each thread: 4 consecutive pixels of one row (one Philox block of normals)
+      for (int idx = threadIdx.x; idx < HB * quads_per_row; idx += BAND_BT) {
+        const int a = idx / quads_per_row, qd = idx - a * quads_per_row, i = r0 + a, jb = 4 * qd;
+        if (i >= g.ny) continue;
+        real z[4] = {0, 0, 0, 0};
+        if (A.noise == nullptr)
+          img_noise4<real>(A.key, A.chain_offset + (unsigned long long)chain, it_global, i, qd, quads_per_row, z);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int j = jb + k;
+          if (j >= g.nx) break;
+          const long long o = (long long)i * g.nx + j;
+          const real xv = xc[o];
+          const real* rr = RR + (a + 1) * pitch + BAND_PAD + j;
+          const real* ss = SS + (a + 1) * pitch + BAND_PAD + j;
+          const real t = ((-rr[0] + rr[-pitch]) - ss[0]) + ss[-1];   // order of sol_at()
+          const real sol = xv - A.tv_gamma * (-t);
+          const real xi = (A.noise != nullptr) ? A.noise[(chain * A.N + n) * g.P + o] : z[k];
+          real gr = A.grad[chain * g.P + o];
+          if (A.gextra != nullptr) gr = gr + A.gscale * A.gextra[chain * g.P + o];   // algs.py:291
+          // algs.py:569: (1 - tau/gamma) x - tau grad f(x) + tau/gamma prox_g(x) + sqrt(2 tau) xi
+          const real xn = A.a_x * xv - A.tau * gr + A.tog * sol + A.s2t * xi;
+          xc[o] = xn;
+          if (A.samples != nullptr) A.samples[(chain * A.N + n) * g.P + o] = xn;
+          if (stats) {
+            real m = A.mean[chain * g.P + o];
+            const real d = xn - m;
+            m += d / cntn;
+            A.mean[chain * g.P + o] = m;
+            if (A.m2 != nullptr) A.m2[chain * g.P + o] += d * (xn - m);
+          }
+        }
+      }
+    }
+  }
+}
+
+template <typename real, int NT>
+__global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid_constant__ MyulaArgs<real> A) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  real* smem = reinterpret_cast<real*>(smem_raw);
+  __shared__ double red[2 * BAND_NW];
+  __shared__ int s_next[2];
+  cg::grid_group grid = cg::this_grid();
+  BandSched sched{A.queue, s_next, 0, 0, 0};
+  if (blockIdx.x == 0 && threadIdx.x < 4) A.queue[threadIdx.x] = gridDim.x;
+  // pad columns (and everything else) zero once; the phases only ever write columns [0, nx)
+  for (int idx = threadIdx.x; idx < (int)(myula_band_smem_bytes<real, NT>(A.pitch) / sizeof(real)); idx += BAND_BT)
+    smem[idx] = real(0);
+  grid.sync();
+  for (long long n = 0; n < A.N; ++n) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
+    mband_grad_sweep0<real, NT>(A, sched, smem, red);
+    grid.sync();
+    phase_tv_scalar(A, 0);
+    grid.sync();
+    for (int it = 1; it < A.tv_niter; ++it) {
+      if (*(volatile int*)A.n_active == 0) break;
+      grid.sync();   // everyone has read n_active before it is reset
+      if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
+      mband_tv_sweep<real>(A, sched, it, smem, red);
+      grid.sync();
+      phase_tv_scalar(A, it);
+      grid.sync();
+    }
+    mband_update<real>(A, sched, n, smem);
+    grid.sync();
+  }
+}
+
+}  // namespace

@@ -146,6 +146,7 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     peaks = roofline.measured_peaks()
     ach = bpp * P * chains * iters / secs / 1e9
     onchip = engine == "onchip" or (engine == "auto" and eng.onchip_supported())
+    band = not onchip and (engine == "band" or (engine == "auto" and eng.myula_band_supported()))
     if onchip:
         kernel = "img_myula_onchip_kernel<32,5,%d>" % (1 if dims == (256, 256) else 0)
         policy = ("chain state resident in the shared memory of an 8-CTA cluster for all iterations of a launch; "
@@ -156,14 +157,14 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
                 "the on-chip kernel removes that traffic (see `traffic`, measured DRAM bytes per launch), so frac can "
                 "exceed 1 and the binding resource is instruction issue (smsp__issue_active in profiles/)")
     else:
-        kernel = "img_myula_kernel<%s>" % ("float" if item == 4 else "double")
+        kernel = ("img_myula_band_kernel<%s,5>" if band else "img_myula_kernel<%s>") % ("float" if item == 4 else "double")
         policy, traffic, note = "per-chain arrays total far more than the 126 MB L2", None, None
     out = {"metric": "myula_deconv_chain_iters_per_sec", "value": world * chains * iters / secs,
            "unit": "chain-iters/s", "n_gpus": world, "pooled_mean_finite": bool(torch.isfinite(pooled).all().item()),
            "pixel_iters_per_sec": world * chains * iters * P / secs, "dtype": dtype, "dims": list(dims),
            "chains": chains,
            "iters_per_launch": iters, "ms_per_launch": secs * 1e3, "tv_sweeps_per_iter": j,
-           "e2e": e2e, "engine": "onchip" if onchip else "stream", "state_bytes": int(10 * chains * P * item), "l2_policy": policy,
+           "e2e": e2e, "engine": "onchip" if onchip else ("band" if band else "stream"), "state_bytes": int(10 * chains * P * item), "l2_policy": policy,
            "roofline": {"bound": "hbm", "kernel": kernel,
                         "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
                         "bytes_per_pixel_iter": bpp, "traffic": traffic, "peak_source": peaks["source"]}}

@@ -322,6 +322,11 @@ class DeconvEngine:
         return {"tv_sweeps": int(c[0]), "lsqr_iterations": int(c[1]), "lsqr_solves": int(c[2])}
 
     # ------------------------------------------------------------------ MYULA
+    def myula_band_supported(self):
+        """True when the row-band MYULA kernel (csrc/img_myula_band.inl) covers this problem."""
+        pb = self._problem()
+        return bool(self.lib.lmc_img_myula_band_supported(C.byref(pb), _dt(self.dtype)))
+
     def onchip_supported(self):
         """True when the on-chip cluster kernel (csrc/img_myula_onchip.cu) covers this problem."""
         pb = self._problem()
@@ -349,7 +354,7 @@ class DeconvEngine:
             nzn = nz[:, n:n + 1].contiguous() if nz is not None else None
             sn = torch.empty((Cn, 1, self.P), dtype=self.tdt, device=self.dev) if samples is not None else None
             keep = self._myula_launch(x, 1, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, nzn, sn,
-                                      mean, m2, burnin, stat_count0, iter_offset + n, "stream", fgrad_extra=gm,
+                                      mean, m2, burnin, stat_count0, iter_offset + n, engine, fgrad_extra=gm,
                                       fgrad_scale=-ncvx.lamda)
             torch.cuda.current_stream(self.dev).synchronize()   # gm / workspace lifetime
             if samples is not None:
@@ -362,16 +367,18 @@ class DeconvEngine:
         """One launch: N iterations of all chains.
 
         ``engine``: "onchip" = cluster kernel with the chain state in shared memory (fp32, images up to
-        256 x 256), "stream" = tiled kernel through HBM (any size, fp32/fp64), "auto" = on-chip when
-        it applies.  Both are CUDA; there is no CPU path."""
+        256 x 256), "band" = row-band kernel through HBM (H5 blur, even width; any height, fp32/fp64),
+        "stream" = 32x32-tile kernel through HBM (any separable blur and size), "auto" = on-chip, else band,
+        else tile.  All are CUDA; there is no CPU path."""
         torch, lib = self.torch, self.lib
         Cn = x.shape[0]
         pr = _lib.ImgMyulaParams()
         pr.tau, pr.gamma, pr.epsg = float(tau), float(gamma), float(epsg)
         pr.tv_sigma, pr.tv_rtol, pr.tv_niter = float(tv_sigma), float(tv_rtol), int(tv_niter)
-        if engine not in ("auto", "onchip", "stream"):
-            raise ValueError("engine must be 'auto', 'onchip' or 'stream'")
+        if engine not in ("auto", "onchip", "band", "stream"):
+            raise ValueError("engine must be 'auto', 'onchip', 'band' or 'stream'")
         onchip = engine == "onchip" or (engine == "auto" and self.onchip_supported() and fgrad_extra is None)
+        band = engine == "band" or (engine == "auto" and not onchip and self.myula_band_supported())
         if onchip:
             ws = torch.empty(256, dtype=torch.uint8, device=self.dev)
         else:
@@ -384,6 +391,7 @@ class DeconvEngine:
             io.d_fgrad_extra, io.fgrad_scale = fgrad_extra.data_ptr(), float(fgrad_scale)
         pb = self._problem()
         fn, name = ((lib.lmc_img_myula_run_onchip, "lmc_img_myula_run_onchip") if onchip
+                    else (lib.lmc_img_myula_run_band, "lmc_img_myula_run_band") if band
                     else (lib.lmc_img_myula_run, "lmc_img_myula_run"))
         with torch.cuda.device(self.dev):
             rc = fn(C.byref(pb), C.byref(pr), _dt(self.dtype), Cn, int(N), seed & (2 ** 64 - 1),

@@ -14,7 +14,9 @@ iters = int(sys.argv[3]) if len(sys.argv) > 3 else 4
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
 if which == "myula":
-    r = deconv_bench.run_myula(dev, steps=2, warmup=1, chains=chains, iters=iters)
+    engine = sys.argv[4] if len(sys.argv) > 4 else "auto"
+    side = int(sys.argv[5]) if len(sys.argv) > 5 else 256
+    r = deconv_bench.run_myula(dev, steps=2, warmup=1, chains=chains, iters=iters, engine=engine, dims=(side, side))
 else:
     engine = sys.argv[4] if len(sys.argv) > 4 else "auto"
     group = int(sys.argv[5]) if len(sys.argv) > 5 else 0

@@ -328,3 +328,52 @@ def test_ulpda_band_work_queue_many_chains(torch, dims, Cn, dtype, tol):
     if dtype == "float64":
         assert out["band"][4] == out["tile"][4]
     assert len({tuple(np.round(out["band"][0][c][:4], 6)) for c in range(Cn)}) == Cn     # chains differ (own noise)
+
+
+@pytest.mark.parametrize("dims", [(64, 64), (40, 52), (23, 30), (70, 96), (9, 4)])
+def test_myula_band_trajectory_fp64(torch, dims):
+    """Row-band MYULA kernel (img_myula_band.inl) against the oracle: ragged last band / sub-band, narrow images."""
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    N = 14
+    pb = _problem(dims, 5)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(2, N, P)
+    tv = pb["tv"]()
+    want = D.MoreauYosidaUnadjustedLangevin(pb["l2"](), tv, pb["x0"], tau=pb["tau_myula"], gamma=pb["gamma_myula"],
+                                            niter=N, noise=noise)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    assert eng.myula_band_supported()
+    z = lambda *s: torch.zeros(s, dtype=torch.float64, device="cuda")
+    x, samples, mean, m2 = z(1, P), z(1, N, P), z(1, P), z(1, P)
+    eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise[None], samples=samples,
+              mean=mean, m2=m2, engine="band")
+    got = samples.cpu().numpy()[0]
+    errs = [rel(got[n], want[n]) for n in range(N)]
+    assert max(errs) < 1e-12, errs
+    assert rel(mean.cpu().numpy()[0], want.mean(axis=0)) < 1e-12
+    assert eng.read_counters()["tv_sweeps"] == sum(min(u + 1, 10) for u in tv.updates)
+
+
+@pytest.mark.parametrize("dims,Cn,dtype,tol", [((48, 40), 150, "float64", 1e-11), ((64, 128), 90, "float32", 1e-5)])
+def test_myula_band_many_chains_match_tile_kernel(torch, dims, Cn, dtype, tol):
+    """More work items than resident CTAs, in-kernel Philox noise, running statistics: band == tile kernel."""
+    from lmc_atomi_b200 import imaging as I
+    N = 4
+    pb = _problem(dims)
+    P = dims[0] * dims[1]
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype=dtype)
+    out = {}
+    for engine in ("stream", "band"):
+        z = lambda *s: torch.zeros(s, dtype=eng.tdt, device="cuda")
+        x, mean, m2 = z(Cn, P), z(Cn, P), z(Cn, P)
+        eng.counters.zero_()
+        eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, seed=11, chain_offset=5, mean=mean, m2=m2,
+                  burnin=1, engine=engine)
+        torch.cuda.synchronize()
+        out[engine] = [t.double().cpu().numpy() for t in (x, mean, m2)] + [eng.read_counters()["tv_sweeps"]]
+    for a, b in zip(out["band"][:2], out["stream"][:2]):
+        assert rel(a, b) < tol
+    assert rel(out["band"][2], out["stream"][2]) < 100 * tol
+    if dtype == "float64":
+        assert out["band"][3] == out["stream"][3]
