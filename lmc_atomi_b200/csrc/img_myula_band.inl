@@ -35,30 +35,44 @@ __device__ __forceinline__ void mband_stage_rr(const MyulaArgs<real>& A, long lo
   const real* qa = dual_ptr(A, it % 3, 1, chain);
   const real* pb = dual_ptr(A, (it + 2) % 3, 0, chain);
   const real* qb = dual_ptr(A, (it + 2) % 3, 1, chain);
+  constexpr int NB = 5;   // rows whose loads are in flight together
   for (int col = MB_W * threadIdx.x; col < g.nx; col += MB_W * BAND_BT) {
-#pragma unroll 5
-    for (int a = 0; a < nrows; ++a) {
-      const int i = r_first + a;
-      P2 r, s;
+    for (int a0 = 0; a0 < nrows; a0 += NB) {
+      P2 p[NB], q2[NB], pp[NB], qq[NB];
+      if (it >= 1) {
 #pragma unroll
-      for (int q = 0; q < MB_W; ++q) r.a[q] = s.a[q] = real(0);
-      if (it >= 1 && i >= 0 && i < g.ny) {
-        const int o = i * g.nx + col;
-        const P2 p = ldp<real, MB_W>(pa + o), q2 = ldp<real, MB_W>(qa + o);
-        if (it >= 2) {
-          const P2 pp = ldp<real, MB_W>(pb + o), qq = ldp<real, MB_W>(qb + o);
-#pragma unroll
-          for (int q = 0; q < MB_W; ++q) {
-            r.a[q] = p.a[q] + c * (p.a[q] - pp.a[q]);
-            s.a[q] = q2.a[q] + c * (q2.a[q] - qq.a[q]);
+        for (int k = 0; k < NB; ++k) {   // rows outside the image are clamped (their values are discarded below)
+          const int o = min(max(r_first + a0 + k, 0), g.ny - 1) * g.nx + col;
+          p[k] = ldp<real, MB_W>(pa + o);
+          q2[k] = ldp<real, MB_W>(qa + o);
+          if (it >= 2) {
+            pp[k] = ldp<real, MB_W>(pb + o);
+            qq[k] = ldp<real, MB_W>(qb + o);
           }
-        } else {   // c_1 = 0 and p_0 = 0
-          r = p;
-          s = q2;
         }
       }
-      stp<real, MB_W>(RR + a * pitch + BAND_PAD + col, r);
-      stp<real, MB_W>(SS + a * pitch + BAND_PAD + col, s);
+#pragma unroll
+      for (int k = 0; k < NB; ++k) {
+        const int a = a0 + k, i = r_first + a;
+        if (a >= nrows) break;
+        P2 r, s;
+#pragma unroll
+        for (int q = 0; q < MB_W; ++q) r.a[q] = s.a[q] = real(0);
+        if (it >= 1 && i >= 0 && i < g.ny) {
+          if (it >= 2) {
+#pragma unroll
+            for (int q = 0; q < MB_W; ++q) {
+              r.a[q] = p[k].a[q] + c * (p[k].a[q] - pp[k].a[q]);
+              s.a[q] = q2[k].a[q] + c * (q2[k].a[q] - qq[k].a[q]);
+            }
+          } else {   // c_1 = 0 and p_0 = 0
+            r = p[k];
+            s = q2[k];
+          }
+        }
+        stp<real, MB_W>(RR + a * pitch + BAND_PAD + col, r);
+        stp<real, MB_W>(SS + a * pitch + BAND_PAD + col, s);
+      }
     }
   }
 }
@@ -80,6 +94,22 @@ __device__ __forceinline__ Pack<real, MB_W> mband_sol(const real* RR, const real
   return out;
 }
 
+// projected dual update of one pixel.  fp64: the reference's divisions (dual_update of the tile kernel).  fp32: the
+// shortcuts of the on-chip kernel, far inside the 1e-5 trajectory tolerance: dx / (8 gamma) is a multiply by the
+// host-rounded reciprocal and r / max(1, |(r,s)|) is r * min(1, rsqrt(r^2 + s^2)).
+template <typename real>
+__device__ __forceinline__ void mband_dual_update(real rr, real ss, real dx, real dy, real g8, real inv_g8, real& p,
+                                                  real& q) {
+  if constexpr (sizeof(real) == 4) {
+    const real r = rr - dx * inv_g8, s = ss - dy * inv_g8;
+    const real w = Math<real>::min(real(1), Math<real>::rsqrt(Math<real>::max(r * r + s * s, real(1e-30))));
+    p = r * w;
+    q = s * w;
+  } else {
+    dual_update(rr, ss, dx, dy, g8, p, q);
+  }
+}
+
 // ---------------------------------------------------------------- phase G (+ sweep 0)
 template <typename real, int NT>
 __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, real* smem, double* red) {
@@ -91,7 +121,7 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
   real* T = smem + Band<real, NT, RB>::XROWS * pitch;
   const real* wx = A.g.wx;
   const real* wy = A.g.wy;
-  const real g8 = real(8) * A.tv_gamma;
+  const real g8 = real(8) * A.tv_gamma, inv_g8 = (real)(1.0 / (8.0 * (double)A.tv_gamma));
   sched.begin();
   for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
@@ -123,7 +153,7 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
         const real dx = (i < g.ny - 1) ? xd.a[q] - xv.a[q] : real(0);
         const real dy = (c + q < g.nx - 1) ? (q + 1 < MB_W ? xv.a[q + 1 < MB_W ? q + 1 : 0] : xright) - xv.a[q] : real(0);
         acc += (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
-        dual_update(real(0), real(0), dx, dy, g8, pn.a[q], qn.a[q]);
+        mband_dual_update(real(0), real(0), dx, dy, g8, inv_g8, pn.a[q], qn.a[q]);
       }
       stp<real, MB_W>(p1 + o, pn);
       stp<real, MB_W>(q1 + o, qn);
@@ -143,7 +173,7 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
   real* RR = smem;                        // local row a <-> image row r0 - 1 + a, a = 0 .. HB + 1
   real* SS = RR + (HB + 2) * pitch;
   real* SOL = SS + (HB + 2) * pitch;      // local row a <-> image row r0 + a, a = 0 .. HB
-  const real g8 = real(8) * A.tv_gamma;
+  const real g8 = real(8) * A.tv_gamma, inv_g8 = (real)(1.0 / (8.0 * (double)A.tv_gamma));
   sched.begin();
   for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
@@ -158,14 +188,16 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
       mband_stage_rr(A, chain, it, r0 - 1, HB + 2, RR, SS);
       __syncthreads();
       for (int col = MB_W * threadIdx.x; col < g.nx; col += MB_W * BAND_BT) {
-#pragma unroll 3
-        for (int a = 0; a <= HB; ++a) {
-          const int i = r0 + a;
-          P2 xv;
+        P2 xr[HB + 1];
 #pragma unroll
-          for (int q = 0; q < MB_W; ++q) xv.a[q] = real(0);
-          if (i < g.ny) xv = ldp<real, MB_W>(xc + i * g.nx + col);
-          stp<real, MB_W>(SOL + a * pitch + BAND_PAD + col, mband_sol(RR, SS, pitch, a + 1, col, xv, A.tv_gamma));
+        for (int a = 0; a <= HB; ++a) xr[a] = ldp<real, MB_W>(xc + min(r0 + a, g.ny - 1) * g.nx + col);
+#pragma unroll
+        for (int a = 0; a <= HB; ++a) {
+          if (r0 + a >= g.ny) {   // below the image: x = 0 (the row is never read by an in-image pixel's dx)
+#pragma unroll
+            for (int q = 0; q < MB_W; ++q) xr[a].a[q] = real(0);
+          }
+          stp<real, MB_W>(SOL + a * pitch + BAND_PAD + col, mband_sol(RR, SS, pitch, a + 1, col, xr[a], A.tv_gamma));
         }
       }
       __syncthreads();
@@ -187,7 +219,7 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
             const real dy = (col + q < g.nx - 1) ? (q + 1 < MB_W ? sv.a[q + 1 < MB_W ? q + 1 : 0] : sright) - sv.a[q] : real(0);
             const real df = xv.a[q] - sv.a[q];
             acc += 0.5 * (double)df * (double)df + (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
-            dual_update(rc.a[q], sc.a[q], dx, dy, g8, po.a[q], qo.a[q]);
+            mband_dual_update(rc.a[q], sc.a[q], dx, dy, g8, inv_g8, po.a[q], qo.a[q]);
           }
           stp<real, MB_W>(pn + o, po);
           stp<real, MB_W>(qn + o, qo);

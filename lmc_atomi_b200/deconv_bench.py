@@ -226,5 +226,10 @@ def run(dev, steps=3, warmup=3, **kw):
     # the general / fp64-validation path, for comparison
     st = run_myula(dev, steps=max(1, min(steps, 2)), warmup=1, engine="stream", **kw)
     out["streaming_kernel"] = {k: st[k] for k in ("value", "unit", "ms_per_launch", "tv_sweeps_per_iter", "roofline")}
+    # the reference's own image size (skimage camera / einstein crop: 512 x 512) does not fit the on-chip kernel:
+    # row-band kernel through HBM
+    big = run_myula(dev, steps=max(1, min(steps, 2)), warmup=1, chains=256, dims=(512, 512), iters=10, engine="band")
+    out["band_kernel_512"] = {k: big[k] for k in ("value", "unit", "dims", "chains", "ms_per_launch",
+                                                   "tv_sweeps_per_iter", "engine", "roofline")}
     out["ulpda"] = run_ulpda(dev, steps=max(1, min(steps, 3)), warmup=min(warmup, 2))
     return out
