@@ -271,54 +271,95 @@ __device__ void band_kb(const UlpdaArgs<real>& A, BandSched& sched, long long c_
   }
 }
 
+// four consecutive pixels of one row as one 16/32-byte access when the rows allow it, else n <= 4 scalar ones
+template <typename real>
+__device__ __forceinline__ Pack<real, 4> band_ld4(const real* p, int n, bool vec) {
+  if (vec) return ldp<real, 4>(p);
+  Pack<real, 4> v;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) v.a[k] = (k < n) ? p[k] : real(0);
+  return v;
+}
+template <typename real>
+__device__ __forceinline__ void band_st4(real* p, const Pack<real, 4>& v, int n, bool vec) {
+  if (vec) {
+    stp<real, 4>(p, v);
+    return;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (k < n) p[k] = v.a[k];
+}
+
 // ---------------------------------------------------------------- Pf: last deferred update, noise, xhat, statistics
 template <typename real, int RB>
 __device__ void band_primal_final(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, long long n) {
+  using P4 = Pack<real, 4>;
   const Geom<real>& g = A.g;
   const int items = (int)(c_hi - c_lo) * g.tiles;
   const int quads_per_row = (g.nx + 3) / 4;
   const unsigned long long it_global = A.iter_offset + (unsigned long long)n;
   const bool stats = (A.mean != nullptr) && ((long long)it_global >= A.burnin);
-  const real inv_cnt = real(1) / (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
   const real cntn = (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
-  (void)inv_cnt;
+  // every array of the phase is touched at the same element offsets: one alignment test for all of them
+  bool vec = (g.nx % 4 == 0);
+  {
+    const void* ptrs[] = {A.warm, A.w, A.x, A.xhat, A.out, A.noise, A.samples, A.mean, A.m2};
+    for (const void* p : ptrs) vec = vec && (reinterpret_cast<size_t>(p) % (4 * sizeof(real)) == 0);
+  }
   sched.begin();
   for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     const LsqrState s = A.st[chain];
     const real t1 = (real)s.t1, sw = (real)s.sw;
+    const bool pending = s.pending != 0;
     for (int idx = threadIdx.x; idx < RB * quads_per_row; idx += BAND_BT) {
       const int a = idx / quads_per_row, qd = idx - a * quads_per_row, i = i0 + a, jb = 4 * qd;
       if (i >= g.ny) continue;
-      real z[4] = {0, 0, 0, 0};
-      if (A.mode == 0 && A.noise == nullptr)
-        img_noise4<real>(A.key, A.chain_offset + (unsigned long long)chain, it_global, i, qd, quads_per_row, z);
+      const int nq = min(4, g.nx - jb);
+      const long long o = chain * g.P + (long long)i * g.nx + jb;
+      const long long os = (chain * A.N + n) * g.P + (long long)i * g.nx + jb;
+      // all loads of the quad first, then the arithmetic
+      P4 zf = band_ld4(A.warm + o, nq, vec), wv, xold, xi, mn, m2v;
+      if (pending) wv = band_ld4(A.w + o, nq, vec);
+      if (A.mode == 0) {
+        xold = band_ld4(A.x + o, nq, vec);
+        if (A.noise != nullptr) xi = band_ld4(A.noise + os, nq, vec);
+        if (stats) {
+          mn = band_ld4(A.mean + o, nq, vec);
+          if (A.m2 != nullptr) m2v = band_ld4(A.m2 + o, nq, vec);
+        }
+        if (A.noise == nullptr)
+          img_noise4<real>(A.key, A.chain_offset + (unsigned long long)chain, it_global, i, qd, quads_per_row, xi.a);
+      }
+      if (pending) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) zf.a[k] += t1 * (sw * wv.a[k]);
+      }
+      band_st4(A.warm + o, zf, nq, vec);
+      if (A.mode == 1) {
+        band_st4(A.out + o, zf, nq, vec);
+        continue;
+      }
+      P4 xn, xh;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const int j = jb + k;
-        if (j >= g.nx) break;
-        const long long o = chain * g.P + (long long)i * g.nx + j;
-        real zf = A.warm[o];
-        if (s.pending) zf += t1 * (sw * A.w[o]);
-        A.warm[o] = zf;
-        if (A.mode == 1) {
-          A.out[o] = zf;
-          continue;
+        xn.a[k] = zf.a[k] + A.s2t * xi.a[k];                      // algs.py:446
+        xh.a[k] = xn.a[k] + A.theta * (xn.a[k] - xold.a[k]);      // algs.py:447
+      }
+      band_st4(A.x + o, xn, nq, vec);
+      band_st4(A.xhat + o, xh, nq, vec);
+      if (A.samples != nullptr) band_st4(A.samples + os, xn, nq, vec);
+      if (stats) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const real d = xn.a[k] - mn.a[k];
+          mn.a[k] += d / cntn;
+          if (A.m2 != nullptr) m2v.a[k] += d * (xn.a[k] - mn.a[k]);
         }
-        const real xi = (A.noise != nullptr) ? A.noise[(chain * A.N + n) * g.P + (long long)i * g.nx + j] : z[k];
-        const real xold = A.x[o];
-        const real xn = zf + A.s2t * xi;                 // algs.py:446
-        A.x[o] = xn;
-        A.xhat[o] = xn + A.theta * (xn - xold);          // algs.py:447
-        if (A.samples != nullptr) A.samples[(chain * A.N + n) * g.P + (long long)i * g.nx + j] = xn;
-        if (stats) {
-          real m = A.mean[o];
-          const real d = xn - m;
-          m += d / cntn;
-          A.mean[o] = m;
-          if (A.m2 != nullptr) A.m2[o] += d * (xn - m);
-        }
+        band_st4(A.mean + o, mn, nq, vec);
+        if (A.m2 != nullptr) band_st4(A.m2 + o, m2v, nq, vec);
       }
     }
   }
@@ -327,8 +368,15 @@ __device__ void band_primal_final(const UlpdaArgs<real>& A, BandSched& sched, lo
 // ---------------------------------------------------------------- Pd: y = proxdual(y + mu G xhat)
 template <typename real, int RB>
 __device__ void band_dual(const UlpdaArgs<real>& A, BandSched& sched, long long c_lo, long long c_hi, long long n) {
+  using P4 = Pack<real, 4>;
   const Geom<real>& g = A.g;
   const int items = (int)(c_hi - c_lo) * g.tiles;
+  const int quads_per_row = (g.nx + 3) / 4;
+  bool vec = (g.nx % 4 == 0);
+  {
+    const void* ptrs[] = {A.xhat, A.y, A.ysamples};
+    for (const void* p : ptrs) vec = vec && (reinterpret_cast<size_t>(p) % (4 * sizeof(real)) == 0);
+  }
   sched.begin();
   for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
@@ -336,17 +384,25 @@ __device__ void band_dual(const UlpdaArgs<real>& A, BandSched& sched, long long 
     const real* xh = A.xhat + chain * g.P;
     real* y0 = A.y + chain * 2 * g.P;
     real* y1 = y0 + g.P;
-    for (int c = threadIdx.x; c < g.nx; c += BAND_BT) {
-      real xv = (i0 < g.ny) ? xh[(long long)i0 * g.nx + c] : real(0);
-#pragma unroll 4
-      for (int k = 0; k < RB; ++k) {
-        const int i = i0 + k;
-        if (i >= g.ny) break;
-        const long long o = (long long)i * g.nx + c;
-        const real xb = (i < g.ny - 1) ? xh[o + g.nx] : real(0);
-        const real d0 = (i < g.ny - 1) ? xb - xv : real(0);
-        const real d1 = (c < g.nx - 1) ? xh[o + 1] - xv : real(0);
-        real v0 = y0[o] + A.mu * d0, v1 = y1[o] + A.mu * d1;   // y + mu * A xhat
+    // a thread owns 4 consecutive pixels of one row: the quad, the quad below and the pixel to its right
+    for (int idx = threadIdx.x; idx < RB * quads_per_row; idx += BAND_BT) {
+      const int a = idx / quads_per_row, qd = idx - a * quads_per_row, i = i0 + a, jb = 4 * qd;
+      if (i >= g.ny) continue;
+      const int nq = min(4, g.nx - jb);
+      const long long o = (long long)i * g.nx + jb;
+      const bool below = i < g.ny - 1;
+      const P4 xc = band_ld4(xh + o, nq, vec);
+      P4 xb = xc;
+      if (below) xb = band_ld4(xh + o + g.nx, nq, vec);
+      const real xr = (jb + 4 < g.nx) ? xh[o + 4] : real(0);
+      const P4 u0 = band_ld4(y0 + o, nq, vec), u1 = band_ld4(y1 + o, nq, vec);
+      P4 r0, r1;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const real xv = xc.a[k];
+        const real d0 = below ? xb.a[k] - xv : real(0);
+        const real d1 = (jb + k < g.nx - 1) ? ((k < 3) ? xc.a[k < 3 ? k + 1 : 0] : xr) - xv : real(0);
+        real v0 = u0.a[k] + A.mu * d0, v1 = u1.a[k] + A.mu * d1;   // y + mu * A xhat
         if (A.isotropic) {   // L21 dual prox: v / max(1, |v|_2 / sigma)
           const real nrm = Math<real>::sqrt(v0 * v0 + v1 * v1);
           const real den = Math<real>::max(real(1), nrm / A.g_sigma);
@@ -356,14 +412,15 @@ __device__ void band_dual(const UlpdaArgs<real>& A, BandSched& sched, long long 
           v0 = Math<real>::max(-A.g_sigma, Math<real>::min(A.g_sigma, v0));
           v1 = Math<real>::max(-A.g_sigma, Math<real>::min(A.g_sigma, v1));
         }
-        y0[o] = v0;
-        y1[o] = v1;
-        if (A.ysamples != nullptr) {
-          real* ys = A.ysamples + (chain * A.N + n) * 2 * g.P;
-          ys[o] = v0;
-          ys[g.P + o] = v1;
-        }
-        xv = xb;
+        r0.a[k] = v0;
+        r1.a[k] = v1;
+      }
+      band_st4(y0 + o, r0, nq, vec);
+      band_st4(y1 + o, r1, nq, vec);
+      if (A.ysamples != nullptr) {
+        real* ys = A.ysamples + (chain * A.N + n) * 2 * g.P;
+        band_st4(ys + o, r0, nq, vec);
+        band_st4(ys + g.P + o, r1, nq, vec);
       }
     }
   }
