@@ -208,7 +208,7 @@ int lmc_img_ulpda_run_band(const lmc_img_problem* pb, const lmc_img_ulpda_params
 
 /* MYULA, row-band formulation (csrc/img_myula_band.inl): bands of 16 full-width rows, fused two-pass H^T H with
  * compile-time taps, TV sweeps on 8-row sub-bands, two columns per thread, work items drawn from a global queue.
- * Same arguments, workspace and results as lmc_img_myula_run; requires the 5 x 5 blur centred at (2, 2), an even
+ * Same arguments, workspace and results as lmc_img_myula_run; requires 5/6/7 blur taps on both axes, an even
  * width and buffers aligned to two elements (lmc_img_myula_band_supported() != 0). */
 int lmc_img_myula_band_supported(const lmc_img_problem* pb, int dtype);
 int lmc_img_myula_run_band(const lmc_img_problem* pb, const lmc_img_myula_params* pr, int dtype, int64_t C,

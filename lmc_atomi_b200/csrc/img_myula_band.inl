@@ -111,9 +111,10 @@ __device__ __forceinline__ void mband_dual_update(real rr, real ss, real dx, rea
 }
 
 // ---------------------------------------------------------------- phase G (+ sweep 0)
-template <typename real, int NT>
+// GW = image columns per thread of this phase (2 when the blur's tap windows start on even columns, else 1)
+template <typename real, int NT, int GW>
 __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, real* smem, double* red) {
-  using P2 = Pack<real, MB_W>;
+  using P2 = Pack<real, GW>;
   constexpr int RB = MB_RB, E = NT - 1;
   const Geom<real>& g = A.g;
   const int pitch = A.pitch, items = (int)A.C * g.tiles;
@@ -131,32 +132,32 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
     real* p1 = dual_ptr(A, 1, 0, chain);
     real* q1 = dual_ptr(A, 1, 1, chain);
     band_stage(X, pitch, A.x + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
-    band_forward<real, NT, RB, MB_W>(g, X, T, pitch, i0, wx, wy,
-                                     [&](int i, int c) { return ldp<real, MB_W>(bc + i * g.nx + c); });
+    band_forward<real, NT, RB, GW>(g, X, T, pitch, i0, wx, wy,
+                                     [&](int i, int c) { return ldp<real, GW>(bc + i * g.nx + c); });
     __syncthreads();
     double acc = 0, none = 0;
-    BandPf<real, MB_W, 0, 4> pf;
-    band_adjoint<real, NT, RB, MB_W, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, P2 (&)[1]) {},
+    BandPf<real, GW, 0, 4> pf;
+    band_adjoint<real, NT, RB, GW, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, P2 (&)[1]) {},
                                            [&](int i, int c, int k, const P2& gv, const P2 (&)[1]) {
       const int o = i * g.nx + c;
       P2 go;
 #pragma unroll
-      for (int q = 0; q < MB_W; ++q) go.a[q] = A.sigma_l2 * gv.a[q];
-      stp<real, MB_W>(gout + o, go);
+      for (int q = 0; q < GW; ++q) go.a[q] = A.sigma_l2 * gv.a[q];
+      stp<real, GW>(gout + o, go);
       // TV sweep 0: rr = ss = 0 -> sol = x, obj = gamma sum |grad x|, p_1 = proj(-grad x / (8 gamma))
       const real* xr = X + (k + E) * pitch + BAND_PAD + c;
-      const P2 xv = ldp<real, MB_W>(xr), xd = ldp<real, MB_W>(xr + pitch);
-      const real xright = xr[MB_W];
+      const P2 xv = ldp<real, GW>(xr), xd = ldp<real, GW>(xr + pitch);
+      const real xright = xr[GW];
       P2 pn, qn;
 #pragma unroll
-      for (int q = 0; q < MB_W; ++q) {
+      for (int q = 0; q < GW; ++q) {
         const real dx = (i < g.ny - 1) ? xd.a[q] - xv.a[q] : real(0);
-        const real dy = (c + q < g.nx - 1) ? (q + 1 < MB_W ? xv.a[q + 1 < MB_W ? q + 1 : 0] : xright) - xv.a[q] : real(0);
+        const real dy = (c + q < g.nx - 1) ? (q + 1 < GW ? xv.a[q + 1 < GW ? q + 1 : 0] : xright) - xv.a[q] : real(0);
         acc += (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
         mband_dual_update(real(0), real(0), dx, dy, g8, inv_g8, pn.a[q], qn.a[q]);
       }
-      stp<real, MB_W>(p1 + o, pn);
-      stp<real, MB_W>(q1 + o, qn);
+      stp<real, GW>(p1 + o, pn);
+      stp<real, GW>(q1 + o, qn);
     });
     band_block_sum2(acc, none, red);
     if (threadIdx.x == 0) A.partial[chain * g.tiles + i0 / RB] = acc;
@@ -290,7 +291,7 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
   }
 }
 
-template <typename real, int NT>
+template <typename real, int NT, int GW>
 __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid_constant__ MyulaArgs<real> A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
@@ -305,7 +306,7 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid
   grid.sync();
   for (long long n = 0; n < A.N; ++n) {
     if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-    mband_grad_sweep0<real, NT>(A, sched, smem, red);
+    mband_grad_sweep0<real, NT, GW>(A, sched, smem, red);
     grid.sync();
     phase_tv_scalar(A, 0);
     grid.sync();

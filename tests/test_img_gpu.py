@@ -330,13 +330,15 @@ def test_ulpda_band_work_queue_many_chains(torch, dims, Cn, dtype, tol):
     assert len({tuple(np.round(out["band"][0][c][:4], 6)) for c in range(Cn)}) == Cn     # chains differ (own noise)
 
 
-@pytest.mark.parametrize("dims", [(64, 64), (40, 52), (23, 30), (70, 96), (9, 4)])
-def test_myula_band_trajectory_fp64(torch, dims):
-    """Row-band MYULA kernel (img_myula_band.inl) against the oracle: ragged last band / sub-band, narrow images."""
+@pytest.mark.parametrize("dims,kernel", [((64, 64), 5), ((40, 52), 5), ((23, 30), 5), ((70, 96), 5), ((9, 4), 5),
+                                         ((40, 52), 6), ((33, 96), 7), ((64, 64), 7)])
+def test_myula_band_trajectory_fp64(torch, dims, kernel):
+    """Row-band MYULA kernel (img_myula_band.inl) against the oracle: ragged last band / sub-band, narrow images,
+    the H6 / H7 blurs (one column per thread in the gradient phase)."""
     from lmc_atomi_b200 import imaging as I
     from oracle import deconv_ref as D
     N = 14
-    pb = _problem(dims, 5)
+    pb = _problem(dims, kernel)
     P = dims[0] * dims[1]
     noise = D.image_noise(2, N, P)
     tv = pb["tv"]()
