@@ -482,14 +482,12 @@ __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch,
   if (STATS) ch.flush();
 }
 
-#ifndef LMC_MIX_MINB
-#define LMC_MIX_MINB 4
-#endif
-// fp32 production chains: LMC_MIX_MINB resident CTAs per SM (register cap 65536 / (256 * MINB)).  Measured on B200
-// (r01e, K=20000, 2^20 chains): 4 -> 170.8, 5 (48 regs) -> 167.9, 6 (40 regs, spills) -> 164.1 G chain-steps/s:
-// the chains are bound by the MUFU/FMA pipes (math-pipe throttle + fixed-latency waits), not by occupancy.
+// Occupancy experiment (r01e, K=20000, 2^20 chains, fp32 production chains): a minimum of 5 resident CTAs per SM
+// (48 registers) gave 167.9, 6 (40 registers, spills) 164.1, and even the hint "4" (which only changes the
+// register allocator's target) 165.8 against 170.8 G chain-steps/s without any hint: the chains are bound by the
+// MUFU/FMA pipes (math-pipe throttle + fixed-latency waits), not by occupancy.  No hint.
 template <typename real, int TARGET, int ALG, int NC, bool PROD>
-__global__ void __launch_bounds__(BLOCK, (PROD && sizeof(real) == 4) ? LMC_MIX_MINB : 1) mix_chain_kernel(const __grid_constant__ MixP<real> P,
+__global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant__ MixP<real> P,
                                                           const __grid_constant__ MixIo io) {
   using M = Math<real>;
   constexpr bool ADJ = AlgTraits<ALG>::adjusted;
