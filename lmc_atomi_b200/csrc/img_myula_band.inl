@@ -185,51 +185,81 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
     real* qn = dual_ptr(A, (it + 1) % 3, 1, chain);
     double acc = 0, none = 0;
     for (int r0 = i0; r0 < i0 + RB && r0 < g.ny; r0 += HB) {
+      // x on the 9 rows of the sub-band (rows below the image clamped, zeroed when used): requested before the
+      // duals are staged, consumed two barriers later by sol and again by the pixel update
+      auto load_x = [&](int col, P2 (&xr)[HB + 1]) {
+#pragma unroll
+        for (int a = 0; a <= HB; ++a) xr[a] = ldp<real, MB_W>(xc + min(r0 + a, g.ny - 1) * g.nx + col);
+      };
+      const int col0 = MB_W * threadIdx.x;
+      P2 xr[HB + 1];
+      if (col0 < g.nx) load_x(col0, xr);
       if (r0 != i0) __syncthreads();   // the previous sub-band's readers are done
       mband_stage_rr(A, chain, it, r0 - 1, HB + 2, RR, SS);
       __syncthreads();
-      for (int col = MB_W * threadIdx.x; col < g.nx; col += MB_W * BAND_BT) {
-        P2 xr[HB + 1];
-#pragma unroll
-        for (int a = 0; a <= HB; ++a) xr[a] = ldp<real, MB_W>(xc + min(r0 + a, g.ny - 1) * g.nx + col);
+      for (int col = col0; col < g.nx; col += MB_W * BAND_BT) {
+        if (col != col0) load_x(col, xr);
 #pragma unroll
         for (int a = 0; a <= HB; ++a) {
+          P2 xv = xr[a];
           if (r0 + a >= g.ny) {   // below the image: x = 0 (the row is never read by an in-image pixel's dx)
 #pragma unroll
-            for (int q = 0; q < MB_W; ++q) xr[a].a[q] = real(0);
+            for (int q = 0; q < MB_W; ++q) xv.a[q] = real(0);
           }
-          stp<real, MB_W>(SOL + a * pitch + BAND_PAD + col, mband_sol(RR, SS, pitch, a + 1, col, xr[a], A.tv_gamma));
+          stp<real, MB_W>(SOL + a * pitch + BAND_PAD + col, mband_sol(RR, SS, pitch, a + 1, col, xv, A.tv_gamma));
         }
       }
       __syncthreads();
-      for (int col = MB_W * threadIdx.x; col < g.nx; col += MB_W * BAND_BT) {
-#pragma unroll 2
+      for (int col = col0; col < g.nx; col += MB_W * BAND_BT) {
+        if (col != col0 || g.nx > MB_W * BAND_BT) load_x(col, xr);   // more than one column group: xr holds the last one
+#pragma unroll
         for (int a = 0; a < HB; ++a) {
           const int i = r0 + a;
-          if (i >= g.ny) break;
-          const int o = i * g.nx + col;
-          const real* sr = SOL + a * pitch + BAND_PAD + col;
-          const P2 sv = ldp<real, MB_W>(sr), sd = ldp<real, MB_W>(sr + pitch), xv = ldp<real, MB_W>(xc + o);
-          const real sright = sr[MB_W];
-          const P2 rc = ldp<real, MB_W>(RR + (a + 1) * pitch + BAND_PAD + col),
-                   sc = ldp<real, MB_W>(SS + (a + 1) * pitch + BAND_PAD + col);
-          P2 po, qo;
+          if (i < g.ny) {
+            const int o = i * g.nx + col;
+            const real* sr = SOL + a * pitch + BAND_PAD + col;
+            const P2 sv = ldp<real, MB_W>(sr), sd = ldp<real, MB_W>(sr + pitch), xv = xr[a];
+            const real sright = sr[MB_W];
+            const P2 rc = ldp<real, MB_W>(RR + (a + 1) * pitch + BAND_PAD + col),
+                     sc = ldp<real, MB_W>(SS + (a + 1) * pitch + BAND_PAD + col);
+            P2 po, qo;
 #pragma unroll
-          for (int q = 0; q < MB_W; ++q) {
-            const real dx = (i < g.ny - 1) ? sd.a[q] - sv.a[q] : real(0);
-            const real dy = (col + q < g.nx - 1) ? (q + 1 < MB_W ? sv.a[q + 1 < MB_W ? q + 1 : 0] : sright) - sv.a[q] : real(0);
-            const real df = xv.a[q] - sv.a[q];
-            acc += 0.5 * (double)df * (double)df + (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
-            mband_dual_update(rc.a[q], sc.a[q], dx, dy, g8, inv_g8, po.a[q], qo.a[q]);
+            for (int q = 0; q < MB_W; ++q) {
+              const real dx = (i < g.ny - 1) ? sd.a[q] - sv.a[q] : real(0);
+              const real dy = (col + q < g.nx - 1) ? (q + 1 < MB_W ? sv.a[q + 1 < MB_W ? q + 1 : 0] : sright) - sv.a[q] : real(0);
+              const real df = xv.a[q] - sv.a[q];
+              acc += 0.5 * (double)df * (double)df + (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
+              mband_dual_update(rc.a[q], sc.a[q], dx, dy, g8, inv_g8, po.a[q], qo.a[q]);
+            }
+            stp<real, MB_W>(pn + o, po);
+            stp<real, MB_W>(qn + o, qo);
           }
-          stp<real, MB_W>(pn + o, po);
-          stp<real, MB_W>(qn + o, qo);
         }
       }
     }
     band_block_sum2(acc, none, red);
     if (threadIdx.x == 0) A.partial[chain * g.tiles + i0 / RB] = acc;
   }
+}
+
+// four consecutive pixels of one row as one 16/32-byte access when the rows allow it, else n <= 4 scalar ones
+template <typename real>
+__device__ __forceinline__ Pack<real, 4> mb_ld4(const real* p, int n, bool vec) {
+  if (vec) return ldp<real, 4>(p);
+  Pack<real, 4> v;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) v.a[k] = (k < n) ? p[k] : real(0);
+  return v;
+}
+template <typename real>
+__device__ __forceinline__ void mb_st4(real* p, const Pack<real, 4>& v, int n, bool vec) {
+  if (vec) {
+    stp<real, 4>(p, v);
+    return;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (k < n) p[k] = v.a[k];
 }
 
 // ---------------------------------------------------------------- phase U
@@ -244,47 +274,62 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
   const unsigned long long it_global = A.iter_offset + (unsigned long long)n;
   const bool stats = (A.mean != nullptr) && ((long long)it_global >= A.burnin);
   const real cntn = (real)(A.stat_count0 + ((long long)it_global - A.burnin) + 1);
+  using P4 = Pack<real, 4>;
+  bool vec = (g.nx % 4 == 0);
+  {
+    const void* ptrs[] = {A.x, A.grad, A.gextra, A.noise, A.samples, A.mean, A.m2};
+    for (const void* p : ptrs) vec = vec && (reinterpret_cast<size_t>(p) % (4 * sizeof(real)) == 0);
+  }
   sched.begin();
   for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
     band_of(g, w, 0, RB, chain, i0);
     const int kf = A.st[chain].kf;
-    real* xc = A.x + chain * g.P;
     for (int r0 = i0; r0 < i0 + RB && r0 < g.ny; r0 += HB) {
       if (r0 != i0) __syncthreads();
       mband_stage_rr(A, chain, kf, r0 - 1, HB + 1, RR, SS);
       __syncthreads();
-      // each thread: 4 consecutive pixels of one row (one Philox block of normals)
+      // each thread: 4 consecutive pixels of one row (one Philox block of normals), moved as one 16/32-byte access
+      // per array when the rows allow it; all loads of the quad are issued before its arithmetic
       for (int idx = threadIdx.x; idx < HB * quads_per_row; idx += BAND_BT) {
         const int a = idx / quads_per_row, qd = idx - a * quads_per_row, i = r0 + a, jb = 4 * qd;
         if (i >= g.ny) continue;
-        real z[4] = {0, 0, 0, 0};
+        const int nq = min(4, g.nx - jb);
+        const long long o = chain * g.P + (long long)i * g.nx + jb;
+        const long long os = (chain * A.N + n) * g.P + (long long)i * g.nx + jb;
+        const P4 xv = mb_ld4(A.x + o, nq, vec), gr0 = mb_ld4(A.grad + o, nq, vec);
+        P4 ge, xi, mn, m2v;
+        if (A.gextra != nullptr) ge = mb_ld4(A.gextra + o, nq, vec);
+        if (A.noise != nullptr) xi = mb_ld4(A.noise + os, nq, vec);
+        if (stats) {
+          mn = mb_ld4(A.mean + o, nq, vec);
+          if (A.m2 != nullptr) m2v = mb_ld4(A.m2 + o, nq, vec);
+        }
         if (A.noise == nullptr)
-          img_noise4<real>(A.key, A.chain_offset + (unsigned long long)chain, it_global, i, qd, quads_per_row, z);
+          img_noise4<real>(A.key, A.chain_offset + (unsigned long long)chain, it_global, i, qd, quads_per_row, xi.a);
+        P4 xn;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const int j = jb + k;
-          if (j >= g.nx) break;
-          const long long o = (long long)i * g.nx + j;
-          const real xv = xc[o];
-          const real* rr = RR + (a + 1) * pitch + BAND_PAD + j;
-          const real* ss = SS + (a + 1) * pitch + BAND_PAD + j;
+          const real* rr = RR + (a + 1) * pitch + BAND_PAD + jb + k;
+          const real* ss = SS + (a + 1) * pitch + BAND_PAD + jb + k;
           const real t = ((-rr[0] + rr[-pitch]) - ss[0]) + ss[-1];   // order of sol_at()
-          const real sol = xv - A.tv_gamma * (-t);
-          const real xi = (A.noise != nullptr) ? A.noise[(chain * A.N + n) * g.P + o] : z[k];
-          real gr = A.grad[chain * g.P + o];
-          if (A.gextra != nullptr) gr = gr + A.gscale * A.gextra[chain * g.P + o];   // algs.py:291
+          const real sol = xv.a[k] - A.tv_gamma * (-t);
+          real gr = gr0.a[k];
+          if (A.gextra != nullptr) gr = gr + A.gscale * ge.a[k];   // algs.py:291
           // algs.py:569: (1 - tau/gamma) x - tau grad f(x) + tau/gamma prox_g(x) + sqrt(2 tau) xi
-          const real xn = A.a_x * xv - A.tau * gr + A.tog * sol + A.s2t * xi;
-          xc[o] = xn;
-          if (A.samples != nullptr) A.samples[(chain * A.N + n) * g.P + o] = xn;
-          if (stats) {
-            real m = A.mean[chain * g.P + o];
-            const real d = xn - m;
-            m += d / cntn;
-            A.mean[chain * g.P + o] = m;
-            if (A.m2 != nullptr) A.m2[chain * g.P + o] += d * (xn - m);
+          xn.a[k] = A.a_x * xv.a[k] - A.tau * gr + A.tog * sol + A.s2t * xi.a[k];
+        }
+        mb_st4(A.x + o, xn, nq, vec);
+        if (A.samples != nullptr) mb_st4(A.samples + os, xn, nq, vec);
+        if (stats) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const real d = xn.a[k] - mn.a[k];
+            mn.a[k] += d / cntn;
+            if (A.m2 != nullptr) m2v.a[k] += d * (xn.a[k] - mn.a[k]);
           }
+          mb_st4(A.mean + o, mn, nq, vec);
+          if (A.m2 != nullptr) mb_st4(A.m2 + o, m2v, nq, vec);
         }
       }
     }
