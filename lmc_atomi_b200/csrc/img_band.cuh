@@ -110,20 +110,29 @@ __device__ __forceinline__ void band_stage(real* S, int pitch, const real* __res
   __syncthreads();
 }
 
-// the NT + W - 1 consecutive elements starting at p (p is W-element aligned)
-template <typename real, int NT, int W>
+// The k x k blurs of the driver (prox_lmc_deconv.py:55-69): first tap of the forward window and the parities of the
+// first shared-memory column the forward / adjoint passes read for an even image column.  Two columns per
+// thread (W = 2) need vector loads from even columns: an odd window start is read from one column earlier.
+template <int NT>
+struct BandWin {
+  static constexpr int LO = (NT == 7) ? -3 : -2;   // pylops pads an even kernel by one trailing zero row / column
+  static constexpr int FWD_OFF = (LO & 1), ADJ_OFF = ((LO + NT - 1) & 1);
+};
+
+// the NT + W - 1 consecutive elements starting at p; p - OFF is W-element aligned
+template <typename real, int NT, int W, int OFF>
 __device__ __forceinline__ void band_taps(const real* p, real (&e)[NT + W - 1]) {
   if constexpr (W == 1) {
 #pragma unroll
     for (int s = 0; s < NT; ++s) e[s] = p[s];
   } else {
-    constexpr int NE = NT + W - 1, NV = (NE + W - 1) / W;
+    constexpr int NE = NT + W - 1, NV = (NE + OFF + W - 1) / W;
 #pragma unroll
     for (int v = 0; v < NV; ++v) {
-      const Pack<real, W> t = ldp<real, W>(p + W * v);
+      const Pack<real, W> t = ldp<real, W>(p - OFF + W * v);
 #pragma unroll
       for (int q = 0; q < W; ++q)
-        if (W * v + q < NE) e[W * v + q] = t.a[q];
+        if (W * v + q >= OFF && W * v + q - OFF < NE) e[W * v + q - OFF] = t.a[q];
     }
   }
 }
@@ -163,7 +172,7 @@ __device__ __forceinline__ void band_adjoint(const Geom<real>& g, const real* T,
 #pragma unroll
     for (int jj = 0; jj < RB + NT - 1; ++jj) {
       real e[NT + W - 1];
-      band_taps<real, NT, W>(trow + jj * pitch, e);
+      band_taps<real, NT, W, (W > 1 ? BandWin<NT>::ADJ_OFF : 0)>(trow + jj * pitch, e);
 #pragma unroll
       for (int q = 0; q < W; ++q) {
         real u = real(0);
@@ -206,7 +215,7 @@ __device__ __forceinline__ void band_forward(const Geom<real>& g, const real* X,
 #pragma unroll
     for (int jj = 0; jj < RB + 2 * (NT - 1); ++jj) {
       real e[NT + W - 1];
-      band_taps<real, NT, W>(xrow + jj * pitch, e);
+      band_taps<real, NT, W, (W > 1 ? BandWin<NT>::FWD_OFF : 0)>(xrow + jj * pitch, e);
 #pragma unroll
       for (int q = 0; q < W; ++q) {
         real t1 = real(0);

@@ -106,10 +106,11 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
     for (const void* p : ptrs)
       LMC_REQUIRE(reinterpret_cast<size_t>(p) % (2 * sizeof(real)) == 0,
                   "MYULA band kernel: buffers must be aligned to two elements");
+    // two columns per thread in the gradient phase when the blur window is the driver's (BandWin)
     switch (pb->ntap_y) {
-      case 5: return pb->lo_x == -2 ? launch_myula_band<real, 5, 2>(A, st) : launch_myula_band<real, 5, 1>(A, st);
-      case 6: return launch_myula_band<real, 6, 1>(A, st);
-      default: return launch_myula_band<real, 7, 1>(A, st);
+      case 5: return pb->lo_x == BandWin<5>::LO ? launch_myula_band<real, 5, 2>(A, st) : launch_myula_band<real, 5, 1>(A, st);
+      case 6: return pb->lo_x == BandWin<6>::LO ? launch_myula_band<real, 6, 2>(A, st) : launch_myula_band<real, 6, 1>(A, st);
+      default: return pb->lo_x == BandWin<7>::LO ? launch_myula_band<real, 7, 2>(A, st) : launch_myula_band<real, 7, 1>(A, st);
     }
   }
   return launch_persistent(img_myula_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);

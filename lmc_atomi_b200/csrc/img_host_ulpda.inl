@@ -26,7 +26,8 @@ bool band_supported(const lmc_img_problem* pb) {
 // band phases touch with vector accesses must be aligned to two elements
 template <typename real>
 bool band_pairs(const UlpdaArgs<real>& A) {
-  if (A.g.ntap_x != 5 || A.g.lo_x != -2 || (A.g.nx & 1)) return false;
+  const int lo = A.g.ntap_x == 7 ? BandWin<7>::LO : BandWin<5>::LO;   // the driver's k x k windows
+  if (A.g.lo_x != lo || (A.g.nx & 1)) return false;
   const void* ptrs[] = {A.x, A.y, A.warm, A.optb, A.u, A.v, A.w, A.in, A.b};
   for (const void* p : ptrs)
     if (reinterpret_cast<size_t>(p) % (2 * sizeof(real)) != 0) return false;
@@ -133,8 +134,8 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
   if (band) {
     switch (pb->ntap_y) {
       case 5: return band_pairs(A) ? launch_band<real, 5, 2>(A, st) : launch_band<real, 5, 1>(A, st);
-      case 6: return launch_band<real, 6, 1>(A, st);
-      default: return launch_band<real, 7, 1>(A, st);
+      case 6: return band_pairs(A) ? launch_band<real, 6, 2>(A, st) : launch_band<real, 6, 1>(A, st);
+      default: return band_pairs(A) ? launch_band<real, 7, 2>(A, st) : launch_band<real, 7, 1>(A, st);
     }
   }
   return launch_persistent(img_ulpda_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);

@@ -178,7 +178,8 @@ def test_myula_trajectory_fp64(torch, dims, kernel):
 
 @pytest.mark.parametrize("engine", ["tile", "band"])
 @pytest.mark.parametrize("dims,kernel,iso,gfirst", [((64, 64), 5, True, False), ((40, 52), 5, False, False),
-                                                    ((33, 95), 6, True, True), ((64, 64), 7, True, False)])
+                                                    ((33, 95), 6, True, True), ((64, 64), 7, True, False),
+                                                    ((40, 52), 6, True, False), ((23, 30), 7, False, True)])
 def test_ulpda_trajectory_fp64(torch, dims, kernel, iso, gfirst, engine):
     from lmc_atomi_b200 import imaging as I
     from oracle import deconv_ref as D
