@@ -88,9 +88,38 @@ def _moreau_term(proxf, dims):
     return imaging.MoreauTerm("me", proxf.lamda, proxf.gamma, True, int(proxf.niter), float(proxf.rtol))
 
 
+NOISE_CHUNK_ITERS = 16    # iterations per launch when the reference's host noise stream is used (pipelined)
+
+
 def _chunk(niter, P, itemsize, arrays):
     per_it = max(1, arrays * P * itemsize)
     return int(max(1, min(niter, CHUNK_BYTES // per_it)))
+
+
+class _NoiseStream:
+    """The reference's noise, ``default_rng(seed).standard_normal(P)`` once per iteration (algs.py:431-433,
+    561-565), drawn in order by a worker thread one chunk ahead of the GPU: the host RNG (the slowest stage of a
+    single-chain run) overlaps the kernels and the copies.  Same stream, same values."""
+
+    def __init__(self, seed, P, chunks):
+        import queue
+        import threading
+        self._q = queue.Queue(maxsize=2)
+        rng = default_rng(seed)
+
+        def work():
+            for n in chunks:
+                self._q.put(rng.standard_normal((1, n, P)))
+
+        self._t = threading.Thread(target=work, daemon=True)
+        self._t.start()
+
+    def next(self):
+        return self._q.get()
+
+
+def _plan(niter, step):
+    return [min(step, niter - d) for d in range(0, niter, step)]
 
 
 def _show_line(iiter, niter):
@@ -119,15 +148,17 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
               'tau = %s\tgamma=%10e\nepsg = %s\tniter = %d\n'
               % (type(proxf), type(proxg), str(tau), gamma, str(epsg), niter))
         print('   Itn       x[0]          f           g     J = f + eps*g')
-    rng = default_rng(seed)
     x = eng._buf(x0, 1)
     out = np.empty((niter, P), dtype=np.float64)
     per_iter = callback is not None or show
     step = 1 if per_iter else _chunk(niter, P, x.element_size(), 2)
+    if not philox and not per_iter:
+        step = min(step, NOISE_CHUNK_ITERS)
+    stream = None if philox else _NoiseStream(seed, P, _plan(niter, step))
     done = 0
     while done < niter:
         n = min(step, niter - done)
-        noise = None if philox else rng.standard_normal((1, n, P))
+        noise = None if philox else stream.next()
         samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
         keep = eng.myula(x, n, tau, gamma, float(proxg.sigma), int(proxg.niter), float(proxg.rtol),
                          epsg=float(epsg), seed=seed, noise=noise, samples=samples, iter_offset=done, ncvx=ncvx)
@@ -188,7 +219,6 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
               (type(proxf), type(proxg), type(A), None if z is None else 'vector',
                str(tau[0]) if fixedtau else 'Variable', str(mu[0]) if fixedmu else 'Variable', theta, niter))
         print('   Itn       x[0]          f         g o A        z^x      U = f + g o A + z^x')
-    rng = default_rng(seed)
     x = eng._buf(x0, 1)
     xhat = x.clone()
     y = eng._buf(y0, 1, inner=2) if y0 is not None else torch.zeros((1, 2, P), dtype=eng.tdt, device=eng.dev)
@@ -200,10 +230,13 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
     need_y = returny or (callback is not None and callbacky)
     per_iter = callback is not None or show or not constant
     step = 1 if per_iter else _chunk(niter, P, x.element_size(), 2 + (2 if need_y else 0))
+    if not philox and not per_iter:
+        step = min(step, NOISE_CHUNK_ITERS)
+    stream = None if philox else _NoiseStream(seed, P, _plan(niter, step))
     done = 0
     while done < niter:
         n = min(step, niter - done)
-        noise = None if philox else rng.standard_normal((1, n, P))
+        noise = None if philox else stream.next()
         samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
         ys = torch.empty((1, n, 2, P), dtype=eng.tdt, device=eng.dev) if need_y else None
         keep = eng.ulpda(x, xhat, y, warm, n, float(tau[done]), float(mu[done]), float(theta), float(proxg.sigma),
