@@ -4,7 +4,8 @@
   tau=0.1125, gamma=0.5625 (prox_lmc_deconv.py:88-94, 465-473), a batch of independent chains
   whose state is far larger than L2;
 * ULPDA deconvolution, 512x512, model M1 (L2(H5, niter=50, warm) + L21(0.3) + Gradient),
-  tau=0.534375, mu=1, theta=1, gfirst=False (prox_lmc_deconv.py:455-464).
+  tau=0.534375, mu=1, theta=1, gfirst=False (prox_lmc_deconv.py:455-464), 512 chains per GPU (BASELINE.json
+  configs[4]: 4096 chains over 8 GPUs).
 
 Synthetic data of the named shapes: a deterministic piecewise-smooth image in [0,255]
 (skimage's camera image is unavailable in this image), blurred by the CUDA H5
@@ -173,7 +174,7 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     return out
 
 
-def run_ulpda(dev, steps=3, warmup=2, chains=256, dims=(512, 512), iters=2, dtype="float32", engine="auto", group=0):
+def run_ulpda(dev, steps=3, warmup=2, chains=512, dims=(512, 512), iters=2, dtype="float32", engine="auto", group=0):
     import torch
     _, eng = make_engine(dims, dev, dtype)
     L = 1.0 / SIGMA ** 2
