@@ -160,6 +160,8 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=20, dt
     else:
         kernel = ("img_myula_band_kernel<%s,5>" if band else "img_myula_kernel<%s>") % ("float" if item == 4 else "double")
         policy, traffic, note = "per-chain arrays total far more than the 126 MB L2", None, None
+        if band and dims == (512, 512) and item == 4:
+            traffic = roofline.MYULA_BAND_DRAM_BYTES_PER_CHAIN_ITER * chains * iters
     out = {"metric": "myula_deconv_chain_iters_per_sec", "value": world * chains * iters / secs,
            "unit": "chain-iters/s", "n_gpus": world, "pooled_mean_finite": bool(torch.isfinite(pooled).all().item()),
            "pixel_iters_per_sec": world * chains * iters * P / secs, "dtype": dtype, "dims": list(dims),

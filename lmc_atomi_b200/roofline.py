@@ -75,3 +75,4 @@ def ulpda_bytes_per_pixel(k_exec: float, itemsize: int = 4) -> float:
 MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 125.2e3, "mala": 104.7e3, "pula": 126.5e3, "mla": 131.6e3}   # state is in registers
 MIX_ISSUE_ACTIVE_PCT = {"ula": 83.0, "mala": 78.3, "pula": 84.4, "mla": 78.3}       # smsp__issue_active, same capture
 ULPDA_BAND_DRAM_BYTES_PER_CHAIN_ITER = (34.459e9 + 23.259e9) / 512.0   # 512x512, H5, k = 8: 256 chains x 2 iterations
+MYULA_BAND_DRAM_BYTES_PER_CHAIN_ITER = (74.037e9 + 36.859e9) / 2560.0   # 512x512, H5, fp32: 256 chains x 10 iterations (r01g)

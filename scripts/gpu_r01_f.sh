@@ -1,6 +1,6 @@
-# round-1 final GPU pass: all GPU tests, smoke, full bench (both arms), launch lists + full captures of the two band kernels
+# round-1 final GPU pass (r01g): all GPU tests, smoke, full bench (both arms), launch lists + full captures of the two band kernels
 set -x
-O=gpurun_out/r01f; mkdir -p $O
+O=gpurun_out/r01g; mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm,memory.total --format=csv > $O/gpu.txt
 timeout 1500 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?" >> $O/smoke.log
