@@ -85,6 +85,21 @@ class LangevinMonteCarloLaplacian(MixtureSampler):
         return sum(self.omegas[i] * self.smooth_multivariate_laplacian(theta, self.mus[i], self.alphas[i])
                    for i in range(len(self.alphas)))
 
+    def true_samples(self):
+        """K draws of the (unsmoothed) Laplacian mixture (lmc_laplace.py:99-107): the component index comes from
+        ``default_rng(seed)``; the Laplace variates come, as in the reference, from numpy's GLOBAL state
+        (``multivariate_laplace.rvs`` is called without ``random_state``, multivariate_laplace.py:436-443), so a
+        caller who wants a reproducible set seeds ``np.random.seed`` first -- the draws then equal the reference's.
+        Host numpy: evaluation data, not on the sampler path."""
+        rng = np.random.default_rng(self.seed)
+        out = np.empty((self.n, self.d))
+        for k in range(self.n):
+            i = rng.integers(0, len(self.mus))
+            _, sv, vt = np.linalg.svd(np.asarray(self.Sigmas[i], dtype=np.float64))   # scipy.linalg.svd: same LAPACK gesdd
+            z = np.random.laplace(loc=0.0, scale=1.0, size=[1, self.d])
+            out[k] = (z @ (np.sqrt(sv)[:, None] * vt) + np.asarray(self.mus[i], dtype=np.float64)).reshape(-1)
+        return out
+
 
 def lmc_laplacian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamma_mla=5e-2, lamda=1e-1, alpha=1e-1,
                           n=5, K=5000, seed=0, dtype="float64"):
@@ -94,7 +109,7 @@ def lmc_laplacian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamm
     X, Y, pos = plot_grid()
     s = LangevinMonteCarloLaplacian(mus, np.ones(n) * alpha, omegas, lamda, K, seed, dtype=dtype)
     out = {"X": X, "Y": Y, "density": s.density_laplacian_mixture(pos),
-           "smooth_density": s.smooth_density_laplacian_mixture(pos)}
+           "smooth_density": s.smooth_density_laplacian_mixture(pos), "true_samples": s.true_samples()}
     out["ula"] = s.ula(gamma_ula)
     out["mala"], out["mala_effective"] = s.mala(gamma_mala)
     out["pula"] = s.pula(gamma_pula, M_PRECONDITIONER)

@@ -38,6 +38,9 @@ def main():
         s = mods["lmc_laplace"].LangevinMonteCarloLaplacian(mus, al, om, 0.1, 10, 0)
         out["laplace"] = s.density_laplacian_mixture(pos)
         out["laplace_smooth"] = s.smooth_density_laplacian_mixture(pos)
+        s = mods["lmc_laplace"].LangevinMonteCarloLaplacian(mus, al, om, 0.1, 40, 2)
+        np.random.seed(1234)            # multivariate_laplace.rvs draws from numpy's global state
+        out["laplace_true_samples"] = s.true_samples()
         mus, Sg, om = refshim.gaussian_mixture_params(5)
         s = mods["prox_lmc"].ProximalLangevinMonteCarlo(mus, Sg, om, 0.25, 0.15, np.zeros(2), 10, 0)
         out["prox"] = s.density_gaussian_mixture(pos) * s.multivariate_laplacian(pos)

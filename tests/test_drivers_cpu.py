@@ -26,6 +26,9 @@ def test_density_helpers_match_reference():
     s = lmc_laplace.LangevinMonteCarloLaplacian(mus, np.ones(5) * 0.5, om, 0.1, 10, 0)
     assert _close(s.density_laplacian_mixture(pos), z["laplace"])
     assert _close(s.smooth_density_laplacian_mixture(pos), z["laplace_smooth"])
+    s = lmc_laplace.LangevinMonteCarloLaplacian(mus, np.ones(5) * 0.5, om, 0.1, 40, 2)
+    np.random.seed(1234)                                  # the reference's rvs() uses numpy's global state
+    assert _close(s.true_samples(), z["laplace_true_samples"])
     mus, Sg, om = lmc.mixture_parameters(5)
     s = prox_lmc.ProximalLangevinMonteCarlo(mus, Sg, om, 0.25, 0.15, np.zeros(2), 10, 0)
     assert _close(s.density_gaussian_mixture(pos) * s.multivariate_laplacian(pos), z["prox"])

@@ -135,7 +135,7 @@ def test_headless_mixture_mains_reproduce_golden_chains():
     out = lmc_laplacian_mixture(0.05, 0.05, 0.05, 0.05, lamda=0.1, alpha=0.5, n=5, K=K, seed=0)
     for a in ("ula", "pula", "mla"):
         assert np.abs(out[a] - l[a][:K]).max() < 1e-11
-    assert out["mala"].shape == (out["mala_effective"], 2)
+    assert out["mala"].shape == (out["mala_effective"], 2) and out["true_samples"].shape == (K, 2)
     p = load_golden("mix_prox.npz")
     out = prox_lmc_gaussian_mixture(0.05, 0.05, 0.05, 0.05, 0.05, 0.05, lamda=0.25, alpha=0.15, n=5, t=100, K=K, seed=0)
     for a in ("pgld", "myula", "ppula", "fbula", "lbmumla"):
