@@ -55,6 +55,11 @@ class MixIo(C.Structure):
                 ("hist_every", C.c_int64), ("burnin", C.c_int64)]
 
 
+class W2Result(C.Structure):
+    _fields_ = [("cost", C.c_double), ("w2", C.c_double), ("eps", C.c_double), ("err", C.c_double),
+                ("mass", C.c_double), ("iters", C.c_int64), ("converged", C.c_int32)]
+
+
 IMG_MAX_TAPS = 16
 
 
@@ -133,6 +138,10 @@ SIGNATURES = {
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "lmc_img_pd_arg": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_int64, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lmc_w2_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
+    "lmc_w2_sinkhorn": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double,
+                                  C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_size_t,
+                                  C.POINTER(W2Result), C.c_void_p]),
 }
 
 _lib = None

@@ -115,10 +115,11 @@ def plot_grid(N=300, lo=-5.0, hi=5.0):
 
 
 def lmc_gaussian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamma_ihpula=5e-2, gamma_mla=5e-2, n=5,
-                         K=5000, seed=0, dtype="float64"):
+                         K=5000, seed=0, dtype="float64", wasserstein=False):
     """Headless ``lmc_gaussian_mixture`` (lmc.py:194-196; same keyword arguments = the CLI flags): runs the five
-    samplers on the CUDA path and returns what the reference goes on to plot.  Plotting, KDE and the POT
-    Wasserstein curves are outside the hot path; ``true_samples`` is returned for them."""
+    samplers on the CUDA path and returns what the reference goes on to plot.  Plotting and KDE are outside the
+    hot path.  ``wasserstein=True`` also evaluates the 2-Wasserstein curves of lmc.py:386-416 on the
+    device (``w2.wasserstein_curves``, Sinkhorn approximation of the exact EMD) into ``out["wasserstein"]``."""
     mus, Sigmas, omegas = mixture_parameters(n)
     X, Y, pos = plot_grid()
     lmc = LangevinMonteCarlo(mus, Sigmas, omegas, K, seed, dtype=dtype)
@@ -128,4 +129,8 @@ def lmc_gaussian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamma
     out["pula"] = lmc.pula(gamma_pula, M_PRECONDITIONER)
     out["ihpula"] = lmc.ihpula(gamma_ihpula)
     out["mla"] = lmc.mla(gamma_mla, BETA_MIRROR)
+    if wasserstein:
+        from . import w2
+        out["wasserstein"] = w2.wasserstein_curves(out["true_samples"],
+                                                   {a: out[a] for a in ("ula", "mala", "pula", "ihpula", "mla")})
     return out

@@ -102,9 +102,11 @@ class LangevinMonteCarloLaplacian(MixtureSampler):
 
 
 def lmc_laplacian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamma_mla=5e-2, lamda=1e-1, alpha=1e-1,
-                          n=5, K=5000, seed=0, dtype="float64"):
+                          n=5, K=5000, seed=0, dtype="float64", wasserstein=False):
     """Headless ``lmc_laplacian_mixture`` (lmc_laplace.py:220-222, same keyword arguments): ULA, MALA, PULA and
-    MLA on the smoothed Laplacian mixture through the CUDA path; returns the arrays the reference plots."""
+    MLA on the smoothed Laplacian mixture through the CUDA path; returns the arrays the reference plots.
+    ``wasserstein=True`` adds the 2-Wasserstein curves of lmc_laplace.py:386-451 (first K1 = 10 000 samples of
+    every set), evaluated on the device by ``w2.wasserstein_curves``."""
     mus, _, omegas = mixture_parameters(n)
     X, Y, pos = plot_grid()
     s = LangevinMonteCarloLaplacian(mus, np.ones(n) * alpha, omegas, lamda, K, seed, dtype=dtype)
@@ -114,4 +116,9 @@ def lmc_laplacian_mixture(gamma_ula=5e-2, gamma_mala=5e-2, gamma_pula=5e-2, gamm
     out["mala"], out["mala_effective"] = s.mala(gamma_mala)
     out["pula"] = s.pula(gamma_pula, M_PRECONDITIONER)
     out["mla"] = s.mla(gamma_mla, BETA_MIRROR)
+    if wasserstein:
+        from . import w2
+        K1 = 10000                                                                   # lmc_laplace.py:387-392
+        out["wasserstein"] = w2.wasserstein_curves(out["true_samples"][:K1],
+                                                   {a: out[a][:K1] for a in ("ula", "mala", "pula", "mla")})
     return out
