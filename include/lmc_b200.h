@@ -273,7 +273,7 @@ int lmc_img_sample_metrics(const lmc_img_problem* pb, int dtype, int isotropic, 
  * (lmc.py:386-416, lmc_laplace.py:426-451).  d_x (n,dim), d_y (m,dim) row-major fp64, dim <= 4.  Log-domain
  * Sinkhorn with epsilon scaling (eps: eps_start -> eps_final by factors eps_scale; eps_start <= 0 = squared
  * diagonal of the joint bounding box), at most max_iters iterations per eps, stopping when the potentials move
- * by less than tol*eps (checked every check_every iterations).  out->cost is the primal value <C, P_eps>,
+ * by less than tol*eps (checked every check_every iterations); omega in [1,2) over-relaxes both updates.  out->cost is the primal value <C, P_eps>,
  * out->w2 its square root: an approximation of the exact EMD that tightens as eps_final -> 0.
  * warm_start != 0 keeps the x-side potentials (first n doubles of the workspace) of the previous call.
  * Unlike the sampler entry points this call SYNCHRONISES the stream (it is an evaluation, with a host loop). */
@@ -284,8 +284,8 @@ typedef struct lmc_w2_result {
 } lmc_w2_result;
 size_t lmc_w2_workspace_bytes(int64_t n, int64_t m);
 int lmc_w2_sinkhorn(const double* d_x, int64_t n, const double* d_y, int64_t m, int32_t dim, double eps_final,
-                    double eps_start, double eps_scale, double tol, int32_t max_iters, int32_t check_every,
-                    int32_t warm_start, void* d_workspace, size_t workspace_bytes, lmc_w2_result* out, void* stream);
+                    double eps_start, double eps_scale, double tol, double omega, int32_t max_iters,
+                    int32_t check_every, int32_t warm_start, void* d_workspace, size_t workspace_bytes, lmc_w2_result* out, void* stream);
 
 #ifdef __cplusplus
 }

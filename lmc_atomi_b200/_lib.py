@@ -140,7 +140,7 @@ SIGNATURES = {
                                  C.c_void_p, C.c_void_p, C.c_void_p]),
     "lmc_w2_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
     "lmc_w2_sinkhorn": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double,
-                                  C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_size_t,
+                                  C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_size_t,
                                   C.POINTER(W2Result), C.c_void_p]),
 }
 

@@ -10,6 +10,7 @@ No CPU path: without the CUDA library / a device the calls raise.
 from __future__ import annotations
 
 import ctypes as C
+import warnings
 
 import numpy as np
 
@@ -21,16 +22,17 @@ EPS_DEFAULT = 1e-3
 class SinkhornW2:
     """Workspace + device copies of a fixed set of ``true_samples``; ``distance(chain)`` evaluates W2 to it."""
 
-    def __init__(self, true_samples, eps=EPS_DEFAULT, eps_scale=0.5, tol=1e-3, max_iters=20000, check_every=16,
-                 device="cuda:0"):
+    def __init__(self, true_samples, eps=EPS_DEFAULT, eps_scale=0.5, tol=1e-3, omega=1.0, max_iters=20000,
+                 check_every=16, device="cuda:0"):
         self.torch = _lib.require_cuda()
         self.lib = _lib.load()
         self.device = self.torch.device(device)
         self.x = self._points(true_samples)
-        self.eps, self.eps_scale, self.tol = float(eps), float(eps_scale), float(tol)
+        self.eps, self.eps_scale, self.tol, self.omega = float(eps), float(eps_scale), float(tol), float(omega)
         self.max_iters, self.check_every = int(max_iters), int(check_every)
         self._ws = None
         self.last = None
+        self.history = []          # one dict per distance() call (iterations, convergence)
 
     def _points(self, a):
         t = self.torch.as_tensor(np.ascontiguousarray(np.asarray(a, dtype=np.float64))) if not self.torch.is_tensor(a) else a
@@ -61,16 +63,21 @@ class SinkhornW2:
             st = self.torch.cuda.current_stream().cuda_stream
             _lib.check(self.lib.lmc_w2_sinkhorn(self.x.data_ptr(), n, y.data_ptr(), m, self.x.shape[1], self.eps,
                                                 float(eps_start) if (warm_start and eps_start) else (4 * self.eps if warm_start else 0.0),
-                                                self.eps_scale, self.tol, self.max_iters, self.check_every,
+                                                self.eps_scale, self.tol, self.omega, self.max_iters, self.check_every,
                                                 1 if warm_start else 0, self._ws.data_ptr(), self._ws.numel() * 8,
                                                 C.byref(res), st), "lmc_w2_sinkhorn")
+        if not res.converged:
+            warnings.warn("lmc_w2_sinkhorn stopped at max_iters=%d with potential change %.3g > tol*eps: the value "
+                          "is an upper estimate" % (self.max_iters, res.err))
         self.last = {"cost": res.cost, "w2": res.w2, "eps": res.eps, "err": res.err, "mass": res.mass,
                      "iters": int(res.iters), "converged": bool(res.converged)}
+        self.history.append(self.last)
         return res.w2
 
-    def curve(self, chain, interval=100, warm_start=True):
+    def curve(self, chain, interval=100, warm_start=False):
         """lmc.py:396-413: W2 to the prefixes ``chain[:k+1]`` for k = 1, 1+interval, ... < K (K = number of true
-        samples), as the reference's ``wass_*_list``."""
+        samples), as the reference's ``wass_*_list``.  Every prefix is a cold start by default: measured at K = 5000,
+        re-using the previous potentials did not lower the iteration count and twice ran into ``max_iters``."""
         y = self._points(chain)
         K = self.x.shape[0]
         out = []
