@@ -96,3 +96,10 @@ def test_headless_main_returns_the_wasserstein_curves():
     for a in ("ula", "mla"):
         want = W.wasserstein2_curve(out["true_samples"], out[a], interval=100)
         assert np.abs(np.array(w[a]) - np.array(want)).max() < TOL
+    from lmc_atomi_b200.lmc_laplace import lmc_laplacian_mixture
+    np.random.seed(7)                                   # the Laplace true samples use numpy's global state
+    out = lmc_laplacian_mixture(0.05, 0.05, 0.05, 0.05, lamda=0.1, alpha=0.5, n=5, K=202, seed=0, wasserstein=True)
+    w = out["wasserstein"]
+    assert set(w) == {"ula", "mala", "pula", "mla"} and len(w["pula"]) == 3
+    want = W.wasserstein2_curve(out["true_samples"], out["pula"], interval=100)
+    assert np.abs(np.array(w["pula"]) - np.array(want)).max() < TOL
