@@ -139,6 +139,15 @@ typedef struct lmc_img_problem {
   int64_t b_chain_stride;   /* 0 = shared, P = per chain */
 } lmc_img_problem;
 
+/* pyproximal.TV.prox semantics, PINNED against the reference's own result figures (oracle/digitise_figs.py,
+ * tests/golden/deconv_curves.npz; evidence in DESIGN.md section 2):
+ *   - the dual FISTA loop is `iter = 0; while iter <= niter`, i.e. at most niter + 1 passes, each starting with
+ *     sol = x - gamma div(rr, ss) and the exit test, so at most niter + 1 evaluations of sol and niter dual updates
+ *     ... + 1: LMC_TV_EXTRA_PASS;
+ *   - the objective of the exit test is 1/2 ||x - sol||^2 + gamma * TV.__call__(sol) and TV.__call__ carries the
+ *     operator's sigma, so the weight of sum |grad sol| is gamma * sigma with gamma = sigma * tau. */
+#define LMC_TV_EXTRA_PASS 1
+
 /* MoreauYosidaUnadjustedLangevin(proxf=L2, proxg=TV(dims, tv_sigma, tv_niter, tv_rtol),
  * tau, gamma, epsg)  (algs.py:477-587) */
 typedef struct lmc_img_myula_params {
@@ -174,8 +183,10 @@ typedef struct lmc_img_io {
   unsigned long long* d_counters; /* (8,) added to: [0] TV sweeps, [1] LSQR iterations, [2] LSQR solves */
   void* d_workspace;
   size_t workspace_bytes;
-  int64_t burnin;           /* global iterations excluded from mean/m2 */
-  int64_t stat_count0;      /* samples already folded into mean/m2 (chunked runs) */
+  int64_t burnin;           /* global iteration index of the first sample folded into mean/m2 */
+  int64_t stat_count0;      /* samples already folded into mean/m2 BEFORE this call (chunked runs): the sample of
+                               global iteration it >= max(burnin, iter_offset) is folded in with count
+                               stat_count0 + (it - max(burnin, iter_offset)) + 1 */
   uint64_t iter_offset;     /* global index of this call's first iteration (Philox counter) */
   /* Non-convex data terms (algs.L2_ncvx_tv, algs.py:22-291): the Moreau-envelope term is evaluated by the
    * unit entry points below between launches, so both need N == 1 (and gfirst == 0 for ULPDA).
@@ -231,9 +242,9 @@ int lmc_img_blur(const lmc_img_problem* pb, int dtype, int adjoint, int64_t C, c
                  void* stream);                                   /* Convolve2D matvec / rmatvec */
 int lmc_img_grad(int dtype, int32_t ny, int32_t nx, int adjoint, int64_t C, const void* d_in, void* d_out,
                  void* stream);                                   /* Gradient: (C,P)->(C,2,P) / adjoint */
-int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, int32_t niter, double rtol, int64_t C,
-                    const void* d_in, void* d_out, unsigned long long* d_counters, void* d_workspace,
-                    size_t workspace_bytes, void* stream);        /* pyproximal.TV.prox with sigma*tau = gamma */
+int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, double sigma, int32_t niter, double rtol,
+                    int64_t C, const void* d_in, void* d_out, unsigned long long* d_counters, void* d_workspace,
+                    size_t workspace_bytes, void* stream);        /* pyproximal.TV(sigma).prox with sigma*tau = gamma */
 int lmc_img_proxdual(int dtype, int isotropic, double sigma, int64_t n_pix, void* d_v, void* stream);
                                                                   /* L21/L1 proxdual, in place on (2,n_pix) */
 int lmc_img_l2_prox(const lmc_img_problem* pb, int dtype, double tau, int32_t iter_lim, double atol, double btol,

@@ -121,7 +121,7 @@ SIGNATURES = {
                                C.c_void_p]),
     "lmc_img_grad": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,
                                C.c_void_p]),
-    "lmc_img_tv_prox": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_int32, C.c_double, C.c_int64,
+    "lmc_img_tv_prox": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_int32, C.c_double, C.c_int64,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "lmc_img_proxdual": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int64, C.c_void_p, C.c_void_p]),
     "lmc_img_l2_prox": (C.c_int, [C.POINTER(ImgProblem), C.c_int, C.c_double, C.c_int32, C.c_double, C.c_double,

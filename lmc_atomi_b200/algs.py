@@ -118,6 +118,45 @@ class _NoiseStream:
         return self._q.get()
 
 
+class _SuppliedNoise:
+    """Validation mode: caller-supplied N(0,1) draws, (niter, P) host array or device tensor, consumed in order."""
+
+    def __init__(self, noise, niter, P):
+        self._z, self._pos = noise, 0
+        if tuple(noise.shape) != (niter, P):
+            raise ValueError(f"noise must have shape (niter, P) = {(niter, P)}, got {tuple(noise.shape)}")
+        self._chunks = None
+
+    def plan(self, chunks):
+        self._chunks = list(chunks)
+        return self
+
+    def next(self):
+        n = self._chunks.pop(0)
+        out = self._z[self._pos:self._pos + n]
+        self._pos += n
+        return out[None] if isinstance(out, np.ndarray) else out.unsqueeze(0)
+
+
+def _noise_source(noise, philox, seed, niter, P, chunks):
+    if philox:
+        return None
+    if noise is not None:
+        return _SuppliedNoise(noise, niter, P).plan(chunks)
+    return _NoiseStream(seed, P, chunks)
+
+
+class _RunningMean:
+    """``reduce="mean"``: the posterior mean the driver takes of the returned samples (prox_lmc_deconv.py:474-475),
+    accumulated on the device by the kernels (Welford), so the (niter, P) samples never cross PCIe."""
+
+    def __init__(self, eng):
+        self.t = eng.torch.zeros((1, eng.P), dtype=eng.tdt, device=eng.dev)
+
+    def result(self):
+        return self.t[0].double().cpu().numpy()
+
+
 def _plan(niter, step):
     return [min(step, niter - d) for d in range(0, niter, step)]
 
@@ -127,10 +166,16 @@ def _show_line(iiter, niter):
 
 
 def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1., niter=10, seed=0,
-                                   callback=None, show=False, dtype="float64", philox=False, device_metrics=None):
+                                   callback=None, show=False, dtype="float64", philox=False, device_metrics=None,
+                                   noise=None, reduce=None):
     """MYULA (algs.py:477-587):
     x <- (1 - tau/gamma) x - tau grad f(x) + tau/gamma prox_{gamma epsg g}(x) + sqrt(2 tau) xi.
-    Returns the (niter, P) float64 array of samples, as the reference does."""
+    Returns the (niter, P) float64 array of samples, as the reference does.
+
+    Extensions (keyword only in spirit; the reference's positional order is unchanged): ``dtype`` arithmetic of
+    the kernels; ``philox`` in-kernel noise instead of the reference's host stream; ``noise`` (niter, P) supplied
+    N(0,1) draws (validation mode); ``device_metrics`` see DeviceMetrics; ``reduce="mean"`` returns the (P,)
+    mean of the samples, accumulated on the device, instead of the samples."""
     _require(tau is not None, "tau=None (the reference itself fails on it at algs.py:569)")
     _require(np.asarray(epsg).size == 1, "vector epsg")
     _require(_kind(proxg) == "TV", f"proxg of type {_kind(proxg)}; supported: pyproximal.TV")
@@ -140,7 +185,7 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
     _require(tuple(int(d) for d in proxg.dims) == eng.dims, "TV dims must equal the image dims")
     x0 = np.asarray(x0, dtype=np.float64)
     P = eng.P
-    if show:
+    if show:   # banner / header / line formats verbatim from algs.py:545-560, 576-583 (output compatibility)
         tstart = time.time()
         print('Moreau--Yosida Unadjusted Langevin\n'
               '---------------------------------------------------------\n'
@@ -148,26 +193,33 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
               'tau = %s\tgamma=%10e\nepsg = %s\tniter = %d\n'
               % (type(proxf), type(proxg), str(tau), gamma, str(epsg), niter))
         print('   Itn       x[0]          f           g     J = f + eps*g')
+    _require(reduce in (None, "mean"), f"reduce={reduce!r}")
     x = eng._buf(x0, 1)
-    out = np.empty((niter, P), dtype=np.float64)
+    rmean = _RunningMean(eng) if reduce == "mean" else None
+    out = np.empty((niter, P), dtype=np.float64) if rmean is None else None
     per_iter = callback is not None or show
+    need_samples = rmean is None or per_iter or device_metrics is not None
     step = 1 if per_iter else _chunk(niter, P, x.element_size(), 2)
     if not philox and not per_iter:
         step = min(step, NOISE_CHUNK_ITERS)
-    stream = None if philox else _NoiseStream(seed, P, _plan(niter, step))
+    stream = _noise_source(noise, philox, seed, niter, P, _plan(niter, step))
     done = 0
     while done < niter:
         n = min(step, niter - done)
-        noise = None if philox else stream.next()
-        samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
+        nz = None if philox else stream.next()
+        samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev) if need_samples else None
         keep = eng.myula(x, n, tau, gamma, float(proxg.sigma), int(proxg.niter), float(proxg.rtol),
-                         epsg=float(epsg), seed=seed, noise=noise, samples=samples, iter_offset=done, ncvx=ncvx)
+                         epsg=float(epsg), seed=seed, noise=nz, samples=samples, iter_offset=done, ncvx=ncvx,
+                         mean=None if rmean is None else rmean.t, stat_count0=done)
         if device_metrics is not None:
             device_metrics._extend(eng.sample_metrics(samples[0], device_metrics.xtrue, float(proxg.sigma), True))
-        out[done:done + n] = samples[0].double().cpu().numpy()   # synchronises the stream
+        if out is not None:
+            out[done:done + n] = samples[0].double().cpu().numpy()   # synchronises the stream
+        else:
+            torch.cuda.current_stream(eng.dev).synchronize()         # workspace / noise lifetime
         del keep
         if per_iter:
-            xh = out[done]
+            xh = out[done] if out is not None else samples[0, 0].double().cpu().numpy()
             if callback is not None:
                 callback(xh)
             if show and _show_line(done, niter):
@@ -177,7 +229,7 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
     if show:
         print('\nTotal time (s) = %.2f' % (time.time() - tstart))
         print('---------------------------------------------------------\n')
-    return out
+    return out if rmean is None else rmean.result()
 
 
 def _is_gradient(A, dims):
@@ -191,10 +243,13 @@ def _is_gradient(A, dims):
 
 def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, theta=1., niter=10,
                                  seed=0, gfirst=True, callback=None, callbacky=False, returny=False,
-                                 show=False, dtype="float64", philox=False, device_metrics=None):
+                                 show=False, dtype="float64", philox=False, device_metrics=None, noise=None,
+                                 reduce=None):
     """ULPDA (algs.py:295-474) for U(x) = f(x) + x^T z + g(Ax) with f = L2 (prox by warm-started
     LSQR), g = L21 / L1 (dual prox = projection), A = forward-difference Gradient.
-    Returns (niter, P) samples [and (niter, 2P) dual samples when ``returny``]."""
+    Returns (niter, P) samples [and (niter, 2P) dual samples when ``returny``].
+    ``dtype``, ``philox``, ``device_metrics``, ``noise``, ``reduce``: as for MoreauYosidaUnadjustedLangevin
+    (``reduce="mean"`` returns the (P,) mean of the x samples; not combined with ``returny``)."""
     eng = _engine(proxf, dtype)
     torch = eng.torch
     P = eng.P
@@ -210,7 +265,7 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
     tau = tau * np.ones(niter, dtype=x0.dtype) if fixedtau else np.asarray(tau, dtype=np.float64)
     mu = mu * np.ones(niter, dtype=x0.dtype) if fixedmu else np.asarray(mu, dtype=np.float64)
     constant = bool(np.all(tau == tau[0]) and np.all(mu == mu[0])) if niter > 0 else True
-    if show:
+    if show:   # banner / header / line formats verbatim from algs.py:410-423, 459-470 (output compatibility)
         tstart = time.time()
         print('Unadjusted Langevin primal-dual: U(x) = f(x) + x^T z + g(Ax)\n'
               '---------------------------------------------------------\n'
@@ -225,39 +280,47 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
     warm_on = bool(getattr(proxf, "warm", True))
     warm = eng._buf(getattr(proxf, "x0", None) if warm_on else None, 1)
     kw = getattr(proxf, "kwargs_solver", None) or {}
-    out = np.empty((niter, P), dtype=np.float64)
+    _require(reduce in (None, "mean") and not (reduce and returny), f"reduce={reduce!r} with returny={returny}")
+    rmean = _RunningMean(eng) if reduce == "mean" else None
+    out = np.empty((niter, P), dtype=np.float64) if rmean is None else None
     outy = np.empty((niter, 2 * P), dtype=np.float64) if returny else None
     need_y = returny or (callback is not None and callbacky)
     per_iter = callback is not None or show or not constant
+    need_samples = rmean is None or per_iter or device_metrics is not None
     step = 1 if per_iter else _chunk(niter, P, x.element_size(), 2 + (2 if need_y else 0))
     if not philox and not per_iter:
         step = min(step, NOISE_CHUNK_ITERS)
-    stream = None if philox else _NoiseStream(seed, P, _plan(niter, step))
+    stream = _noise_source(noise, philox, seed, niter, P, _plan(niter, step))
     done = 0
     while done < niter:
         n = min(step, niter - done)
-        noise = None if philox else stream.next()
-        samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev)
+        nz = None if philox else stream.next()
+        samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev) if need_samples else None
         ys = torch.empty((1, n, 2, P), dtype=eng.tdt, device=eng.dev) if need_y else None
         keep = eng.ulpda(x, xhat, y, warm, n, float(tau[done]), float(mu[done]), float(theta), float(proxg.sigma),
                          iso, gfirst, int(proxf.niter), warm_start=warm_on, atol=kw.get("atol", 1e-6),
-                         btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=z, seed=seed, noise=noise,
-                         samples=samples, ysamples=ys, iter_offset=done, ncvx=ncvx)
+                         btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=z, seed=seed, noise=nz,
+                         samples=samples, ysamples=ys, iter_offset=done, ncvx=ncvx,
+                         mean=None if rmean is None else rmean.t, stat_count0=done)
         if device_metrics is not None:
             device_metrics._extend(eng.sample_metrics(samples[0], device_metrics.xtrue, float(proxg.sigma), iso))
-        out[done:done + n] = samples[0].double().cpu().numpy()
+        if out is not None:
+            out[done:done + n] = samples[0].double().cpu().numpy()
+        else:
+            torch.cuda.current_stream(eng.dev).synchronize()
         if need_y:
             yh = ys[0].double().cpu().numpy().reshape(n, 2 * P)
             if returny:
                 outy[done:done + n] = yh
         del keep
+        if per_iter and (callback is not None or show):
+            xh = out[done] if out is not None else samples[0, 0].double().cpu().numpy()
         if callback is not None:
             if callbacky:
-                callback(out[done], yh[0])
+                callback(xh, yh[0])
             else:
-                callback(out[done])
+                callback(xh)
         if show and _show_line(done, niter):
-            xh = out[done]
             pf, pg = proxf(xh), proxg(A.matvec(xh))
             pf = 0. if type(pf) == bool else pf
             pg = 0. if type(pg) == bool else pg
@@ -271,6 +334,8 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
     if show:
         print('\nTotal time (s) = %.2f' % (time.time() - tstart))
         print('---------------------------------------------------------\n')
+    if rmean is not None:
+        return rmean.result()
     if not returny:
         return out
     return out, outy

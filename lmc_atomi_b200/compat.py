@@ -173,7 +173,7 @@ class TV(ProxOperator):
 
     def prox(self, x, tau):
         x = np.asarray(x)
-        out = imaging.tv_prox(self.dims, _dev(x, (1, -1)), self.sigma * tau, self.niter, self.rtol)
+        out = imaging.tv_prox(self.dims, _dev(x, (1, -1)), self.sigma * tau, self.niter, self.rtol, sigma=self.sigma)
         return out.cpu().numpy().reshape(x.shape)
 
 

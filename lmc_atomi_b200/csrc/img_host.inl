@@ -76,8 +76,10 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
   A.chain_offset = chain_offset;
   A.iter_offset = io->iter_offset;
   A.burnin = io->burnin;
-  A.stat_count0 = io->stat_count0;
-  A.tv_niter = pr->tv_niter;
+  // samples folded in by this call before global iteration `it` = it - max(burnin, iter_offset); the kernels evaluate
+  // count = stat_base + (it - burnin) + 1, so stat_base absorbs the part of iter_offset beyond the burn-in
+  A.stat_count0 = io->stat_count0 - ((long long)io->iter_offset > io->burnin ? (long long)io->iter_offset - io->burnin : 0);
+  A.tv_passes = pr->tv_niter + LMC_TV_EXTRA_PASS;
   A.tv_rtol = pr->tv_rtol;
   if (mode == 0) {
     A.x = (real*)io->d_x;
@@ -95,10 +97,12 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
     A.tog = (real)(pr->tau / pr->gamma);
     A.s2t = (real)sqrt(2 * pr->tau);
     A.tv_gamma = (real)(pr->tv_sigma * (pr->epsg * pr->gamma));   // TV.prox(x, epsg*gamma): sigma * tau
+    A.tv_objw = (double)A.tv_gamma * pr->tv_sigma;                 // obj = .5|x-sol|^2 + gamma * TV.__call__(sol)
   } else {
     A.x = (real*)const_cast<void*>(tv_in);
     A.out = (real*)tv_out;
-    A.tv_gamma = (real)pr->tv_sigma;   // caller passes gamma = sigma * tau here
+    A.tv_gamma = (real)pr->tv_sigma;   // lmc_img_tv_prox passes gamma = sigma * tau here ...
+    A.tv_objw = (double)A.tv_gamma * pr->epsg;   // ... and the operator's sigma here
   }
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
   if (band) {
@@ -173,11 +177,11 @@ extern "C" int lmc_img_myula_run_band(const lmc_img_problem* pb, const lmc_img_m
                           : run_myula<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true);
 }
 
-extern "C" int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, int32_t niter, double rtol,
-                               int64_t C, const void* d_in, void* d_out, unsigned long long* d_counters,
+extern "C" int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, double sigma, int32_t niter,
+                               double rtol, int64_t C, const void* d_in, void* d_out, unsigned long long* d_counters,
                                void* d_workspace, size_t workspace_bytes, void* stream) {
   LMC_REQUIRE(dtype == LMC_F32 || dtype == LMC_F64, "lmc_img_tv_prox: bad dtype");
-  LMC_REQUIRE(ny >= 1 && nx >= 1 && C >= 0 && niter >= 0 && gamma > 0, "lmc_img_tv_prox: bad arguments");
+  LMC_REQUIRE(ny >= 1 && nx >= 1 && C >= 0 && niter >= 0 && gamma > 0 && sigma > 0, "lmc_img_tv_prox: bad arguments");
   if (C == 0) return 0;
   LMC_REQUIRE(d_in != nullptr && d_out != nullptr, "lmc_img_tv_prox: null buffer");
   lmc_img_problem pb;
@@ -185,6 +189,7 @@ extern "C" int lmc_img_tv_prox(int dtype, int32_t ny, int32_t nx, double gamma, 
   lmc_img_myula_params pr;
   memset(&pr, 0, sizeof(pr));
   pr.tv_sigma = gamma;
+  pr.epsg = sigma;
   pr.tv_niter = niter;
   pr.tv_rtol = rtol;
   lmc_img_io io;

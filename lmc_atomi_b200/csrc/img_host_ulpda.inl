@@ -97,7 +97,9 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
   A.chain_offset = chain_offset;
   A.iter_offset = io->iter_offset;
   A.burnin = io->burnin;
-  A.stat_count0 = io->stat_count0;
+  // samples folded in by this call before global iteration `it` = it - max(burnin, iter_offset); the kernels evaluate
+  // count = stat_base + (it - burnin) + 1, so stat_base absorbs the part of iter_offset beyond the burn-in
+  A.stat_count0 = io->stat_count0 - ((long long)io->iter_offset > io->burnin ? (long long)io->iter_offset - io->burnin : 0);
   A.b = (const real*)pb->d_b;
   A.b_stride = pb->b_chain_stride;
   A.warm = (real*)io->d_warm;

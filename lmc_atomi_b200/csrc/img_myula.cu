@@ -49,8 +49,9 @@ struct MyulaArgs {
   unsigned long long chain_offset, iter_offset;
   uint2 key;
   real sigma_l2, tau, a_x, tog, s2t, tv_gamma;
-  int tv_niter;
+  int tv_passes;     // executed passes of the TV loop at most: niter + LMC_TV_EXTRA_PASS (`while iter <= niter`)
   double tv_rtol;
+  double tv_objw;    // weight of sum |grad sol| in the objective of the exit test: gamma * sigma_TV (see lmc_b200.h)
   int mode;  // 0 = MYULA, 1 = TV prox only (out = prox_{tv_gamma TV}(x))
   // band kernel only (img_myula_band.inl)
   int pitch;        // shared-memory row pitch in elements
@@ -118,7 +119,7 @@ __device__ void phase_grad_sweep0(const MyulaArgs<real>& A, real* smem, double* 
         real xv = X[(e + a) * RS + e + bcol];
         real dx = (i < g.ny - 1) ? X[(e + a + 1) * RS + e + bcol] - xv : real(0);
         real dy = (j < g.nx - 1) ? X[(e + a) * RS + e + bcol + 1] - xv : real(0);
-        acc += (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
+        acc += A.tv_objw * (double)Math<real>::sqrt(dx * dx + dy * dy);
         real p, q;
         dual_update(real(0), real(0), dx, dy, g8, p, q);
         p1[(long long)i * g.nx + j] = p;
@@ -147,7 +148,7 @@ __device__ void phase_tv_scalar(const MyulaArgs<real>& A, int it) {
       double rel = s > 1e-10 ? fabs(s - prev) / s : 2.0;
       st.prev_obj = s;
       st.kf = it;
-      st.active = (rel < A.tv_rtol || it == A.tv_niter - 1) ? 0 : 1;
+      st.active = (rel < A.tv_rtol || it == A.tv_passes - 1) ? 0 : 1;
       A.st[chain] = st;
       if (st.active) atomicAdd(A.n_active, 1);
       atomicAdd(A.counters, 1ull);
@@ -236,7 +237,7 @@ __device__ void phase_tv_sweep(const MyulaArgs<real>& A, int it, real* smem, dou
         real dx = (i < g.ny - 1) ? SOL[(a + 1) * PT + bcol] - sv : real(0);
         real dy = (j < g.nx - 1) ? SOL[a * PT + bcol + 1] - sv : real(0);
         real df = X[a * PT + bcol] - sv;
-        acc += 0.5 * (double)df * (double)df + (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
+        acc += 0.5 * (double)df * (double)df + A.tv_objw * (double)Math<real>::sqrt(dx * dx + dy * dy);
         real p, q;
         dual_update(RR[(a + 1) * PT + bcol + 1], SS[(a + 1) * PT + bcol + 1], dx, dy, g8, p, q);
         pn[(long long)i * g.nx + j] = p;
@@ -318,7 +319,7 @@ __global__ void __launch_bounds__(NTHREADS) img_myula_kernel(const __grid_consta
     grid.sync();
     phase_tv_scalar(A, 0);
     grid.sync();
-    for (int it = 1; it < A.tv_niter; ++it) {
+    for (int it = 1; it < A.tv_passes; ++it) {
       if (*(volatile int*)A.n_active == 0) break;
       grid.sync();   // everyone has read n_active before it is reset
       if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;

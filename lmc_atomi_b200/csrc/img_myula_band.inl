@@ -153,7 +153,7 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
       for (int q = 0; q < GW; ++q) {
         const real dx = (i < g.ny - 1) ? xd.a[q] - xv.a[q] : real(0);
         const real dy = (c + q < g.nx - 1) ? (q + 1 < GW ? xv.a[q + 1 < GW ? q + 1 : 0] : xright) - xv.a[q] : real(0);
-        acc += (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
+        acc += A.tv_objw * (double)Math<real>::sqrt(dx * dx + dy * dy);
         mband_dual_update(real(0), real(0), dx, dy, g8, inv_g8, pn.a[q], qn.a[q]);
       }
       stp<real, GW>(p1 + o, pn);
@@ -228,7 +228,7 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
               const real dx = (i < g.ny - 1) ? sd.a[q] - sv.a[q] : real(0);
               const real dy = (col + q < g.nx - 1) ? (q + 1 < MB_W ? sv.a[q + 1 < MB_W ? q + 1 : 0] : sright) - sv.a[q] : real(0);
               const real df = xv.a[q] - sv.a[q];
-              acc += 0.5 * (double)df * (double)df + (double)A.tv_gamma * (double)Math<real>::sqrt(dx * dx + dy * dy);
+              acc += 0.5 * (double)df * (double)df + A.tv_objw * (double)Math<real>::sqrt(dx * dx + dy * dy);
               mband_dual_update(rc.a[q], sc.a[q], dx, dy, g8, inv_g8, po.a[q], qo.a[q]);
             }
             stp<real, MB_W>(pn + o, po);
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid
     grid.sync();
     phase_tv_scalar(A, 0);
     grid.sync();
-    for (int it = 1; it < A.tv_niter; ++it) {
+    for (int it = 1; it < A.tv_passes; ++it) {
       if (*(volatile int*)A.n_active == 0) break;
       grid.sync();   // everyone has read n_active before it is reset
       if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;

@@ -80,8 +80,9 @@ struct OcArgs {
   unsigned long long chain_offset, iter_offset;
   uint2 key;
   float sigma_l2, tau, a_x, tog, s2t, tv_gamma, inv_g8;
-  int tv_niter;
+  int tv_passes;    // niter + LMC_TV_EXTRA_PASS
   double tv_rtol;
+  double tv_objw;   // gamma * sigma_TV: weight of sum |grad sol| in the objective of the exit test
 };
 
 // c_it = (t_{it-1} - 1) / t_it with t_k = t_{k-1} + 1/2, t_0 = 1 (fista_c() of img_myula.cu,
@@ -146,7 +147,7 @@ struct OcCtx {
 // FULL: the image fills the cluster's 8*RPC x 256 footprint (no in-image masks).
 template <int RPC, bool FIRST, bool FULL>
 __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, int cur_ss, int nxt_rr, int nxt_ss,
-                                              float cn, float gamma, float inv_g8,
+                                              float cn, float gamma, double objw, float inv_g8,
                                               float (&P)[RPC / OC_SPLIT], float (&Q)[RPC / OC_SPLIT]) {
   constexpr int STRIP = RPC / OC_SPLIT;
   const int c = K.c, a0 = K.a0;
@@ -197,7 +198,7 @@ __device__ __forceinline__ double oc_tv_sweep(const OcCtx<RPC>& K, int cur_rr, i
       accn += nrm;
     }
     if ((k & 3) == 3) {          // fp32 over 4 pixels, then fp64
-      acc = fma((double)gamma, (double)accn, acc);
+      acc = fma(objw, (double)accn, acc);
       if (!FIRST) acc = fma(0.5, (double)accd, acc);
       accn = accd = 0.0f;
     }
@@ -410,10 +411,10 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
         const int nxt_rr = (it & 1) ? L::Y_RR : L::X_RR, nxt_ss = (it & 1) ? L::Y_SS : L::X_SS;
         double acc;
         if (it == 0) {
-          acc = oc_tv_sweep<RPC, true, FULL>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, 0.0f, gamma, inv_g8, P, Q);
+          acc = oc_tv_sweep<RPC, true, FULL>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, 0.0f, gamma, A.tv_objw, inv_g8, P, Q);
         } else {
-          acc = oc_tv_sweep<RPC, false, FULL>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, oc_fista_c(it + 1), gamma, inv_g8,
-                                              P, Q);
+          acc = oc_tv_sweep<RPC, false, FULL>(K, cur_rr, cur_ss, nxt_rr, nxt_ss, oc_fista_c(it + 1), gamma, A.tv_objw,
+                                              inv_g8, P, Q);
         }
         acc = lmc_warp_sum(acc);
         if (lane == 0) red[wid] = acc;
@@ -437,7 +438,7 @@ __global__ void __launch_bounds__(OC_NT, 1) img_myula_onchip_kernel(const __grid
         prev_obj = obj;
         kf = it;
         ++sweeps_done;
-        if (small || it + 1 >= A.tv_niter) break;
+        if (small || it + 1 >= A.tv_passes) break;
       }
 
       // ============================================================ update
@@ -615,7 +616,9 @@ extern "C" int lmc_img_myula_run_onchip(const lmc_img_problem* pb, const lmc_img
   A.C = C;
   A.N = N;
   A.burnin = io->burnin;
-  A.stat_count0 = io->stat_count0;
+  // samples folded in by this call before global iteration `it` = it - max(burnin, iter_offset); the kernels evaluate
+  // count = stat_base + (it - burnin) + 1, so stat_base absorbs the part of iter_offset beyond the burn-in
+  A.stat_count0 = io->stat_count0 - ((long long)io->iter_offset > io->burnin ? (long long)io->iter_offset - io->burnin : 0);
   A.chain_offset = chain_offset;
   A.iter_offset = io->iter_offset;
   A.key = img_key(seed);
@@ -626,7 +629,8 @@ extern "C" int lmc_img_myula_run_onchip(const lmc_img_problem* pb, const lmc_img
   A.s2t = (float)sqrt(2 * pr->tau);
   A.tv_gamma = (float)(pr->tv_sigma * (pr->epsg * pr->gamma));
   A.inv_g8 = (float)(1.0 / (8.0 * (double)A.tv_gamma));
-  A.tv_niter = pr->tv_niter;
+  A.tv_passes = pr->tv_niter + LMC_TV_EXTRA_PASS;
+  A.tv_objw = (double)A.tv_gamma * pr->tv_sigma;
   A.tv_rtol = pr->tv_rtol;
   cudaStream_t st = (cudaStream_t)stream;
   switch (pb->ntap_y) {

@@ -140,8 +140,15 @@ def proxdual(v, sigma, isotropic=True):
     return v
 
 
-def tv_prox(dims, x, gamma, niter=10, rtol=1e-4, counters=None):
-    """pyproximal.TV.prox with sigma*tau = gamma on device tensors (C,P) or (P,)."""
+def _folded(burnin, iter_offset, n):
+    """Samples a chunked run starting at global iteration ``iter_offset`` has folded into the running mean before
+    its n-th iteration (lmc_img_io::stat_count0 counts the samples folded in BEFORE a launch)."""
+    return max(0, int(iter_offset) + int(n) - max(int(burnin), int(iter_offset)))
+
+
+def tv_prox(dims, x, gamma, niter=10, rtol=1e-4, counters=None, sigma=1.0):
+    """pyproximal.TV(dims, sigma, niter, rtol).prox with sigma*tau = gamma on device tensors (C,P) or (P,).
+    ``sigma`` enters only the objective of the early-exit test (gamma * sigma * sum |grad sol|, see lmc_b200.h)."""
     torch = _lib.require_cuda()
     lib = _lib.load()
     P = dims[0] * dims[1]
@@ -151,7 +158,7 @@ def tv_prox(dims, x, gamma, niter=10, rtol=1e-4, counters=None):
     nb = lib.lmc_img_myula_workspace_bytes(_dt(dt), dims[0], dims[1], x2.shape[0])
     ws = torch.empty(nb, dtype=torch.uint8, device=x2.device)
     with torch.cuda.device(x2.device):
-        rc = lib.lmc_img_tv_prox(_dt(dt), dims[0], dims[1], float(gamma), int(niter), float(rtol), x2.shape[0],
+        rc = lib.lmc_img_tv_prox(_dt(dt), dims[0], dims[1], float(gamma), float(sigma), int(niter), float(rtol), x2.shape[0],
                                  x2.data_ptr(), out.data_ptr(),
                                  counters.data_ptr() if counters is not None else None, ws.data_ptr(), nb,
                                  _stream(torch, x2.device))
@@ -354,8 +361,8 @@ class DeconvEngine:
             nzn = nz[:, n:n + 1].contiguous() if nz is not None else None
             sn = torch.empty((Cn, 1, self.P), dtype=self.tdt, device=self.dev) if samples is not None else None
             keep = self._myula_launch(x, 1, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, nzn, sn,
-                                      mean, m2, burnin, stat_count0, iter_offset + n, engine, fgrad_extra=gm,
-                                      fgrad_scale=-ncvx.lamda)
+                                      mean, m2, burnin, stat_count0 + _folded(burnin, iter_offset, n),
+                                      iter_offset + n, engine, fgrad_extra=gm, fgrad_scale=-ncvx.lamda)
             torch.cuda.current_stream(self.dev).synchronize()   # gm / workspace lifetime
             if samples is not None:
                 samples[:, n] = sn[:, 0]
@@ -428,7 +435,8 @@ class DeconvEngine:
             ysn = torch.empty((Cn, 1, 2, self.P), dtype=self.tdt, device=self.dev) if ysamples is not None else None
             keep = self._ulpda_launch(x, xhat, y, warm, 1, tau, mu, theta, g_sigma, isotropic, False, lsqr_iter_lim,
                                       warm_start, atol, btol, conlim, None, seed, chain_offset, nzn, sn, ysn, mean, m2,
-                                      burnin, stat_count0, iter_offset + n, engine, group, prox_arg=arg)
+                                      burnin, stat_count0 + _folded(burnin, iter_offset, n), iter_offset + n, engine,
+                                      group, prox_arg=arg)
             torch.cuda.current_stream(self.dev).synchronize()
             if samples is not None:
                 samples[:, n] = sn[:, 0]

@@ -34,7 +34,12 @@ def load_image(image):
 
 def prox_lmc_deconv(gamma_mc=15., gamma_me=15., sigma=0.75, tau=0.3, N=1000, niter_l2=50, niter_tv=10,
                     niter_MAP=1000, image='camera', alg='ULPDA', compute_MAP=False, seed=0, models=MODELS,
-                    dtype="float64"):
+                    dtype="float64", noise=None):
+    """Keyword arguments of prox_lmc_deconv.py:40-42, plus ``models`` (subset of MODELS), ``dtype`` of the kernels
+    and ``noise``: the (N, P) N(0,1) draws shared by all models (every sampler call of the driver re-seeds
+    ``default_rng(seed)``, algs.py:431,561, so all nine models see the same stream; passing it once, e.g. as a
+    device tensor, avoids drawing it nine times).  Returns a dict: per model the posterior mean, the per-sample
+    metric curves of the driver's callback (:128-133) and the PSNR of the mean (:707-735)."""
     if compute_MAP:
         raise NotImplementedError("the MAP branch (PDHG, prox_lmc_deconv.py:138-445) is an optimiser outside the "
                                   "sampler hot path; there is no CUDA path for it")
@@ -70,12 +75,13 @@ def prox_lmc_deconv(gamma_mc=15., gamma_me=15., sigma=0.75, tau=0.3, N=1000, nit
         if alg == "ULPDA":
             g = l1 if term == "mc" else l1iso          # the driver pairs MC-TV with the anisotropic prior (:542)
             s = algs.UnadjustedLangevinPrimalDual(f, g, Gop, tau=tau0, mu=mu0, theta=1., x0=x0, gfirst=False,
-                                                  niter=N, seed=seed, dtype=dtype, device_metrics=dm)
+                                                  niter=N, seed=seed, dtype=dtype, device_metrics=dm, noise=noise,
+                                                  reduce="mean")
         else:
             s = algs.MoreauYosidaUnadjustedLangevin(f, tv, tau=tau_myula, gamma=gamma_myula, x0=x0, niter=N,
-                                                    seed=seed, dtype=dtype, device_metrics=dm)
-        mean = s.mean(axis=0)                                                  # :474-475
-        del s
+                                                    seed=seed, dtype=dtype, device_metrics=dm, noise=noise,
+                                                    reduce="mean")
+        mean = s                                                               # samples.mean(axis=0) of :474-475
         out["models"][f"{term}_{k}"] = {
             "mean": mean.reshape(ny, nx), "cost_l2_plus_g": dm.cost, "err": dm.err, "snr": dm.snr, "psnr": dm.psnr,
             "mse": dm.mse, "mean_psnr": float(10 * np.log10(255. ** 2 / np.mean((mean - img.ravel()) ** 2)))}

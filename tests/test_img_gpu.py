@@ -108,7 +108,7 @@ def test_tv_prox_matches_oracle(torch, dims, gamma, niter):
     sweeps = 0
     for c in range(3):
         want, nupd = D.tv_prox_2d(xs[c], gamma, niter, 1e-4)
-        sweeps += min(nupd + 1, niter)
+        sweeps += min(nupd + 1, niter + D.TV_EXTRA_PASS)
         assert rel(got[c], want.ravel()) < 1e-12, (c, nupd)
     assert int(counters[0].item()) == sweeps     # per-chain early exit reproduced
 
@@ -173,7 +173,7 @@ def test_myula_trajectory_fp64(torch, dims, kernel):
     assert max(errs) < 1e-12, errs
     assert rel(mean.cpu().numpy()[0], want.mean(axis=0)) < 1e-12
     assert rel(m2.cpu().numpy()[0] / N, want.var(axis=0)) < 1e-10
-    assert eng.read_counters()["tv_sweeps"] == sum(min(u + 1, 10) for u in tv.updates)
+    assert eng.read_counters()["tv_sweeps"] == sum(min(u + 1, 10 + D.TV_EXTRA_PASS) for u in tv.updates)
 
 
 @pytest.mark.parametrize("engine", ["tile", "band"])
@@ -355,7 +355,7 @@ def test_myula_band_trajectory_fp64(torch, dims, kernel):
     errs = [rel(got[n], want[n]) for n in range(N)]
     assert max(errs) < 1e-12, errs
     assert rel(mean.cpu().numpy()[0], want.mean(axis=0)) < 1e-12
-    assert eng.read_counters()["tv_sweeps"] == sum(min(u + 1, 10) for u in tv.updates)
+    assert eng.read_counters()["tv_sweeps"] == sum(min(u + 1, 10 + D.TV_EXTRA_PASS) for u in tv.updates)
 
 
 @pytest.mark.parametrize("dims,Cn,dtype,tol", [((48, 40), 150, "float64", 1e-11), ((64, 128), 90, "float32", 1e-5)])
