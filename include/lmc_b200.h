@@ -146,7 +146,9 @@ typedef struct lmc_img_problem {
  *     ... + 1: LMC_TV_EXTRA_PASS;
  *   - the objective of the exit test is 1/2 ||x - sol||^2 + gamma * TV.__call__(sol) and TV.__call__ carries the
  *     operator's sigma, so the weight of sum |grad sol| is gamma * sigma with gamma = sigma * tau. */
+#ifndef LMC_TV_EXTRA_PASS
 #define LMC_TV_EXTRA_PASS 1
+#endif
 
 /* MoreauYosidaUnadjustedLangevin(proxf=L2, proxg=TV(dims, tv_sigma, tv_niter, tv_rtol),
  * tau, gamma, epsg)  (algs.py:477-587) */

@@ -93,3 +93,17 @@ def test_roofline_counts():
     assert abs(R.issue_peak_laneops(1965.0) - 148 * 128 * 1.965e9) < 1
     p = R.measured_peaks()
     assert p["hbm_gbs"] > 1000 and p["source"] in ("measured", "fallback")
+
+
+def test_product_package_never_imports_the_oracle():
+    """The oracle is test infrastructure: no module of the product package may import it."""
+    import os
+    import re
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lmc_atomi_b200")
+    bad = []
+    for name in sorted(os.listdir(pkg)):
+        if name.endswith(".py"):
+            src = open(os.path.join(pkg, name)).read()
+            if re.search(r"^\s*(from\s+oracle\b|import\s+oracle\b)", src, flags=re.M):
+                bad.append(name)
+    assert not bad, bad

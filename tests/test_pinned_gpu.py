@@ -14,10 +14,11 @@ pytestmark = pytest.mark.gpu
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 N = 1000
-# Trajectories of N = 1000 iterations: LSQR stops (atol/btol) and TV early exits are data-dependent decisions, and
-# the reference ran another numpy/scipy/FFT build; agreement is asserted at 2e-5 dB (100x the plot resolution,
-# 2500x below the 0.05 dB the north star asks of the posterior-mean PSNR).
-DB_TOL = 2e-5
+# Measured on B200 (profiles/r02b_pinned_*_niter_plus_1_passes.json): every vertex of all 54 curves within 1.3e-7 dB,
+# i.e. the resolution of the plot, over the whole N = 1000 run.  The same run with `niter` instead of `niter + 1` TV
+# passes (LMC_TV_EXTRA_PASS=0, profiles/r02b_pinned_*_niter_passes.json) misses the ME-TV models by 1e-5..3e-5 dB
+# and the MYULA L2/MC-TV models by up to 4.6e-7 dB -- the gate below separates the two.
+DB_TOL = 3e-7
 MODEL_OF = {("l2", 5): 1, ("mc", 5): 2, ("me", 5): 3, ("l2", 6): 4, ("mc", 6): 5, ("me", 6): 6,
             ("l2", 7): 7, ("mc", 7): 8, ("me", 7): 9}      # legend order of prox_lmc_deconv.py:813-821
 
