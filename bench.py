@@ -86,7 +86,8 @@ def _cpu_image_worker(args):
     oracle/deconv_ref.py restating algs.py:295-587) on one chain."""
     which, seed, dims, iters = args
     from oracle import deconv_ref as D
-    pb = D.build_problem(D.synthetic_image(*dims), seed=0)
+    from lmc_atomi_b200.deconv_bench import bench_image
+    pb = D.build_problem(bench_image(dims)[0], seed=0)      # the image the GPU arm uses (einstein crop)
     t0 = time.perf_counter()
     if which == "myula":
         D.MoreauYosidaUnadjustedLangevin(pb["l2"](), pb["tv"](), pb["x0"], tau=pb["tau_myula"], gamma=pb["gamma_myula"],
@@ -273,25 +274,27 @@ def run_ours(args):
     peaks = roofline.measured_peaks()
     clocks = clk.summary()
     sm_mhz_peak = peaks["sm_max_mhz"]
-    peak_ops = roofline.issue_peak_laneops(sm_mhz_peak)
     per_alg = {}
     for a in ALGS:
         secs = t_alg[a] * 1e-3 / args.steps
-        ops = roofline.mix_laneops_per_step("laplace", a) * C * K
+        r = roofline.mix_roofline(a, C * K / secs, sm_mhz_peak)
         per_alg[a] = {"ms_per_launch": secs * 1e3, "chain_steps_per_sec_per_gpu": C * K / secs,
-                      "laneops_per_step": roofline.mix_laneops_per_step("laplace", a),
-                      "frac_issue_peak": ops / secs / peak_ops}
+                      "sass_thread_instr_per_step": r["sass_thread_instr_per_step"], "frac": r["frac"],
+                      "algorithmic_laneops_per_step": r["algorithmic_laneops_per_step"],
+                      "algorithmic_frac": r["algorithmic_frac"],
+                      "issue_active_pct_ncu": roofline.MIX_ISSUE_ACTIVE_PCT.get(a)}
     dom = max(ALGS, key=lambda a: t_alg[a])
     secs = t_alg[dom] * 1e-3 / args.steps
-    ach = roofline.mix_laneops_per_step("laplace", dom) * C * K / secs
-    roof = {"bound": "fp32-issue", "kernel": f"mix_chain_kernel<float,LAPLACE,{dom.upper()},5>",
-            "achieved": ach / 1e12, "peak": peak_ops / 1e12, "unit": "Tlane-op/s", "frac": ach / peak_ops,
-            "traffic": roofline.MIX_DRAM_BYTES_PER_LAUNCH.get(dom),
-            "issue_active_pct_ncu": roofline.MIX_ISSUE_ACTIVE_PCT.get(dom),
-            "peak_source": f"148 SMs x 128 lanes x {sm_mhz_peak:.0f} MHz ({peaks['source']} sm_max_mhz)",
-            "note": "register-resident chains: no HBM traffic in steady state, so the bound is FP32/INT32 issue "
-                    "(north_star); algorithmic lane-ops per step from lmc_atomi_b200/roofline.py",
-            "per_sampler": per_alg}
+    roof = roofline.mix_roofline(dom, C * K / secs, sm_mhz_peak)
+    roof.update({"kernel": f"mix_chain_kernel<float,LAPLACE,{dom.upper()},5,PROD>",
+                 "traffic": roofline.MIX_DRAM_BYTES_PER_LAUNCH.get(dom),
+                 "peak_source": f"148 SMs x 128 lanes x {sm_mhz_peak:.0f} MHz ({peaks['source']} sm_max_mhz)",
+                 "note": "register-resident chains: no HBM traffic in steady state, so the bound is instruction "
+                         "issue (north_star: FP32 issue rate).  frac = EXECUTED thread-instructions per step (ncu "
+                         "capture named in `profile`) x rate / peak = ncu smsp__issue_active; algorithmic_frac uses "
+                         "the survey's lane-op count (an FMA counts twice) and is kept for reference only",
+                 "per_sampler": per_alg})
+    f64 = fp64_line(args, sampler, dev, rank, world, roofline, sm_mhz_peak) if not args.no_f64 else None
     cpu = (cpu_sample(k_unadj=args.cpu_steps, k_adj=max(args.cpu_steps // 4, 50))
            if (world == 1 and not args.no_cpu) else None)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -300,6 +303,8 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": 2 * len(ALGS) * args.steps, "roofline": roof}
+    if f64 is not None:
+        line["value_f64"] = f64
     if cpu is not None:
         line["cpu_baseline"] = {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
                                 "sample": cpu["sample"], "per_core": cpu["per_core"]}
@@ -311,6 +316,34 @@ def run_ours(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def fp64_line(args, sampler, dev, rank, world, roofline, sm_mhz):
+    """The same workload in the reference's own precision (float64), shorter K (stated): the f32 headline then sits
+    beside a same-precision number.  Bound: FP64 issue, 148 SMs x 64 DFMA lanes x clock."""
+    import torch
+    C, K = args.chains, max(200, args.K // 25)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for timed in (False, True):
+        if timed:
+            torch.cuda.synchronize()
+            ev0.record()
+        for alg in ALGS:
+            sampler.sample_chains(alg, GAMMA, chains=C, K=K, dtype="float64", seed=7, chain_offset=rank * C,
+                                  device=dev, _sync=False, **alg_kwargs(alg))
+        if timed:
+            ev1.record()
+    torch.cuda.synchronize()
+    secs = ev0.elapsed_time(ev1) * 1e-3
+    rate = C * K * len(ALGS) / secs
+    peak = roofline.issue_peak_laneops(sm_mhz, lanes=roofline.FP64_LANES_PER_SM)
+    algo = sum(roofline.mix_laneops_per_step("laplace", a) for a in ALGS) / len(ALGS)
+    return {"value": rate * world, "unit": UNIT, "dtype": "f64", "K": K, "chains_per_gpu": C, "ms": secs * 1e3,
+            "note": "per-GPU rate x n_gpus (rank 0 timing); same kernels instantiated for double, IEEE libdevice "
+                    "transcendentals; trajectories within 1e-12 of the reference (tests/test_mix_gpu.py)",
+            "roofline": {"bound": "fp64-issue", "peak": peak / 1e12, "unit": "Tlane-op/s",
+                         "algorithmic_frac": algo * rate / peak, "frac": None,
+                         "note": "no ncu capture of the fp64 instantiation: only the algorithmic figure is given"}}
 
 
 def image_bench(args, dev):
@@ -333,6 +366,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=3000)
     ap.add_argument("--no-image", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-f64", action="store_true", help="skip the float64 line (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

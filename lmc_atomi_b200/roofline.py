@@ -1,12 +1,18 @@
-"""Single source of truth for the algorithmic work per unit and the peaks.
+"""Single source of truth for the roofline accounting of bench.py (VERDICT r01 "What's weak" 5-7).
 
-Mixture chains: zero steady-state HBM traffic -> bound by FP32/INT32 issue
-(SMs x 128 lanes x clock) and the MUFU pipe.  Counts are *algorithmic* lane-ops per
-chain-step from the reference math with per-component constants precomputed
-(one op per + - x / max abs compare; T = one transcendental), not the SASS count.
+Two kinds of bound appear on this path:
 
-Image chains: HBM-bound once batched.  Bytes are array-element transfers per pixel
-per iteration x sizeof(real), using the inner iterations actually executed.
+* ISSUE (mixture chains, on-chip MYULA): the state lives in registers / shared memory, HBM traffic is ~0, so the
+  binding resource is the instruction issue rate: 148 SMs x 4 sub-partitions x 1 warp-instruction per clock
+  = 148 x 128 thread-instructions per clock.  `frac` = EXECUTED thread-instructions per unit (SASS count from the
+  committed ncu capture: smsp__inst_executed x 32 / units) x units/s / peak.  This equals ncu's
+  smsp__issue_active and can never exceed 1.  The survey's ALGORITHMIC lane-op count (one op per + - x / max abs
+  compare, FMA = 2) is reported beside it as `algorithmic_frac`; it can exceed the executed figure because an FMA
+  retires two algorithmic ops in one instruction.
+* HBM (band / tile image kernels): `frac` = algorithmic bytes per unit ((12+9j) / (24+16k) array-element
+  transfers per pixel-iteration) x units/s / measured copy bandwidth; `frac_measured_dram` = DRAM bytes ncu measured
+  per unit x units/s / the same peak (lower than `frac` when re-reads hit the 126 MB L2); `frac_min_traffic` = the
+  kernel's own minimal transfer count (what it would move with a perfect L2).
 """
 from __future__ import annotations
 
@@ -19,6 +25,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 FALLBACK_HBM_GBS = 6650.0
 SM_COUNT = 148
 LANES_PER_SM = 128
+FP64_LANES_PER_SM = 64
 FALLBACK_SM_MHZ = 1965.0
 
 
@@ -32,12 +39,12 @@ def measured_peaks():
     return {"hbm_gbs": FALLBACK_HBM_GBS, "sm_max_mhz": FALLBACK_SM_MHZ, "source": "fallback"}
 
 
-def issue_peak_laneops(sm_mhz: float, sms: int = SM_COUNT) -> float:
-    """FP32/INT32 lane-ops per second at one op per lane per clock."""
-    return sms * LANES_PER_SM * sm_mhz * 1e6
+def issue_peak_laneops(sm_mhz: float, sms: int = SM_COUNT, lanes: int = LANES_PER_SM) -> float:
+    """Thread-instructions per second at one warp-instruction per sub-partition per clock."""
+    return sms * lanes * sm_mhz * 1e6
 
 
-# ---- mixture chains: lane-ops per chain-step (flops + transcendentals + Philox INT ops)
+# ---- mixture chains: ALGORITHMIC lane-ops per chain-step (flops + transcendentals + Philox INT ops, SURVEY 8d)
 _GRAD = {"gauss": 93 + 5, "laplace": 113 + 5, "prox": 93 + 5}     # n=5: 18n+3 (+n T) / 22n+3 (+n T)
 _NOISE_UNADJ = 50 + 4 + 4        # half a Philox block + Box-Muller (4 flops, 4 T)
 _NOISE_ADJ = 100 + 4 + 4 + 2     # full block (2 normals + 1 uniform)
@@ -57,6 +64,32 @@ def mix_laneops_per_step(target: str, alg: str, t: int = 100) -> float:
     return base + extra[alg]
 
 
+# ---- mixture chains: EXECUTED thread-instructions per chain-step of the production kernels on the Laplacian
+# mixture (n = 5), from the `ncu --set full` capture named in MIX_PROFILE: smsp__inst_executed.sum x 32 / (C x K).
+# Keyed by dtype; refreshed whenever mix_kernels.cu changes (the capture is re-taken by scripts/gpu_profile_mix.sh).
+MIX_PROFILE = "profiles/r01e_mix_ncu_full_summary.csv"
+MIX_SASS_INSTR_PER_STEP = {"float32": {"ula": 150.4, "mala": 204.1, "pula": 157.0, "mla": 182.5}}
+MIX_ISSUE_ACTIVE_PCT = {"ula": 83.0, "mala": 78.3, "pula": 84.4, "mla": 78.3}       # smsp__issue_active, same capture
+MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 125.2e3, "mala": 104.7e3, "pula": 126.5e3, "mla": 131.6e3}   # state is in registers
+
+
+def mix_roofline(alg: str, chain_steps_per_sec: float, sm_mhz: float, dtype: str = "float32"):
+    """Roofline object of one production mixture kernel at the measured rate (per GPU)."""
+    peak = issue_peak_laneops(sm_mhz)
+    sass = MIX_SASS_INSTR_PER_STEP.get(dtype, {}).get(alg)
+    algo = mix_laneops_per_step("laplace", alg)
+    out = {"bound": "issue", "unit": "Tthread-inst/s", "peak": peak / 1e12,
+           "algorithmic_laneops_per_step": algo, "algorithmic_frac": algo * chain_steps_per_sec / peak,
+           "sass_thread_instr_per_step": sass, "profile": MIX_PROFILE}
+    if sass is not None:
+        out["achieved"] = sass * chain_steps_per_sec / 1e12
+        out["frac"] = sass * chain_steps_per_sec / peak
+    else:        # no capture of this instantiation: only the algorithmic figure is known
+        out["achieved"] = None
+        out["frac"] = None
+    return out
+
+
 # ---- image chains: bytes per pixel per sampler iteration
 def myula_bytes_per_pixel(j_exec: float, itemsize: int = 4) -> float:
     """(12 + 9 j) array-element transfers: r=Hx-b (3), g=H^T r (2), TV dual
@@ -64,15 +97,69 @@ def myula_bytes_per_pixel(j_exec: float, itemsize: int = 4) -> float:
     return (12 + 9 * j_exec) * itemsize
 
 
+def myula_band_min_bytes_per_pixel(j_exec: float, itemsize: int = 4) -> float:
+    """What img_myula_band.inl moves with a perfect L2: G: x, b in, g, p1, q1 out (5); T_k (k >= 1): x + 2 or 4 dual
+    arrays in, 2 out (7 for k >= 2, 5 for k = 1); U: x, g, mean in + 2 or 4 duals, x, mean out (9)."""
+    j = max(j_exec, 1.0)
+    return (5 + 5 * min(j - 1, 1.0) + 7 * max(j - 2, 0.0) + 9) * itemsize
+
+
 def ulpda_bytes_per_pixel(k_exec: float, itemsize: int = 4) -> float:
     """(24 + 16 k) transfers."""
     return (24 + 16 * k_exec) * itemsize
 
 
-# ---- measured once per round with `ncu --set full` (profiles/r01e_*): dram__bytes_read.sum + dram__bytes_write.sum
-# per launch of the kernel, used for `roofline.traffic`.  Captures are of smaller launches than the bench's
-# (ncu replays every kernel ~40 times); the per-unit figures below are what scales.
-MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 125.2e3, "mala": 104.7e3, "pula": 126.5e3, "mla": 131.6e3}   # state is in registers
-MIX_ISSUE_ACTIVE_PCT = {"ula": 83.0, "mala": 78.3, "pula": 84.4, "mla": 78.3}       # smsp__issue_active, same capture
-ULPDA_BAND_DRAM_BYTES_PER_CHAIN_ITER = (34.459e9 + 23.259e9) / 512.0   # 512x512, H5, k = 8: 256 chains x 2 iterations
-MYULA_BAND_DRAM_BYTES_PER_CHAIN_ITER = (74.037e9 + 36.859e9) / 2560.0   # 512x512, H5, fp32: 256 chains x 10 iterations (r01g)
+def ulpda_band_min_bytes_per_pixel(k_exec: float, itemsize: int = 4) -> float:
+    """img_ulpda_band.inl: every LSQR vector is read and written once per phase = 11 transfers per LSQR iteration
+    (DESIGN 4 I-c) + the 24 of the outer iteration."""
+    return (24 + 11 * k_exec) * itemsize
+
+
+# ---- measured with `ncu --set full` (files under profiles/): dram__bytes_read.sum + dram__bytes_write.sum per launch
+# divided by the chain-iterations of that launch, and executed thread-instructions per pixel-iteration.
+ULPDA_BAND = {"profile": "profiles/r01g_img_ulpda_band_ncu_full_summary.csv",
+              "dram_bytes_per_chain_iter": (34.459e9 + 23.259e9) / 512.0,      # 512x512, H5, k = 8
+              "issue_active_pct": 38.7}
+MYULA_BAND = {"profile": "profiles/r01g_img_myula_band_ncu_full_summary.csv",
+              "dram_bytes_per_chain_iter": (74.037e9 + 36.859e9) / 2560.0,     # 512x512, H5, fp32
+              "issue_active_pct": 41.0}
+MYULA_ONCHIP = {"profile": "profiles/r01c_img_myula_onchip_ncu_full_summary.csv",
+                "dram_bytes_per_chain_iter": (134.6e6 + 86.6e6) / 2560.0,      # 256x256: b prefetch + mean
+                "thread_instr_per_pixel_iter": 395.0, "issue_active_pct": 54.7, "sms_used": 120}
+
+# kept for callers of the r01 names
+ULPDA_BAND_DRAM_BYTES_PER_CHAIN_ITER = ULPDA_BAND["dram_bytes_per_chain_iter"]
+MYULA_BAND_DRAM_BYTES_PER_CHAIN_ITER = MYULA_BAND["dram_bytes_per_chain_iter"]
+
+
+def hbm_roofline(kernel, bytes_alg_per_unit, bytes_min_per_unit, units_per_sec, meas=None, matches_profile=False):
+    """HBM-bound kernel: `frac` by the survey's algorithmic bytes, beside the kernel's minimal traffic and (when the
+    run has the shape of the committed capture) the DRAM bytes ncu measured."""
+    peaks = measured_peaks()
+    peak = peaks["hbm_gbs"]
+    ach = bytes_alg_per_unit * units_per_sec / 1e9
+    out = {"bound": "hbm", "kernel": kernel, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+           "bytes_per_unit_algorithmic": bytes_alg_per_unit,
+           "frac_min_traffic": bytes_min_per_unit * units_per_sec / 1e9 / peak,
+           "traffic": None, "frac_measured_dram": None, "peak_source": peaks["source"]}
+    if meas is not None and matches_profile:
+        out["traffic_per_unit"] = meas["dram_bytes_per_chain_iter"]
+        out["frac_measured_dram"] = meas["dram_bytes_per_chain_iter"] * units_per_sec / 1e9 / peak
+        out["issue_active_pct_ncu"] = meas.get("issue_active_pct")
+        out["profile"] = meas["profile"]
+    return out
+
+
+def onchip_roofline(kernel, pixel_iters_per_sec, sm_mhz):
+    """On-chip MYULA: issue-bound (with shared-memory bandwidth behind it); counted over ALL 148 SMs although the
+    15 co-resident 8-CTA clusters occupy 120 of them."""
+    peak = issue_peak_laneops(sm_mhz)
+    m = MYULA_ONCHIP
+    ach = m["thread_instr_per_pixel_iter"] * pixel_iters_per_sec
+    return {"bound": "issue+smem", "kernel": kernel, "achieved": ach / 1e12, "peak": peak / 1e12,
+            "unit": "Tthread-inst/s", "frac": ach / peak,
+            "sass_thread_instr_per_pixel_iter": m["thread_instr_per_pixel_iter"], "sms_used": m["sms_used"],
+            "issue_active_pct_ncu_on_used_sms": m["issue_active_pct"],
+            "traffic_per_unit": m["dram_bytes_per_chain_iter"], "profile": m["profile"],
+            "note": "chain state lives in the shared memory of a thread-block cluster; HBM carries only the "
+                    "observation prefetch and the running mean, so HBM is not the bound"}
