@@ -270,6 +270,21 @@ int lmc_img_metv_combine(int dtype, int64_t n, double base, double scale, double
 int lmc_img_pd_arg(int dtype, int32_t ny, int32_t nx, double tau, int64_t C, const void* d_x, const void* d_y,
                    const void* d_z, void* d_out, void* stream);
 
+/* MAP branch of the driver (prox_lmc_deconv.py:138-445): pyproximal.optimization.primaldual.AdaptivePrimalDual with
+ * A = Gradient.  One image (C = 1).  The host loop (lmc_atomi_b200/primaldual.py) calls lmc_img_pd_arg and
+ * lmc_img_l2_prox for the primal step, then
+ * lmc_img_pdhg_dual:         Ax <- G x (in place over the previous Ax, (2,P)); y <- proxdual_{L21|L1}(y + mu (2 Ax -
+ *                            Ax_old), mu) in place ((2,P)); *d_resid = ||(y_old - y)/mu - (Ax_old - Ax)||_2
+ * lmc_img_pdhg_primal_resid: ATy <- G^T y (in place over the previous ATy, (P,));
+ *                            *d_resid = ||(x_old - x)/tau - (ATy_old - ATy)||_2
+ * (fp64 sums in a fixed order; d_resid is a device double). */
+size_t lmc_img_pdhg_workspace_bytes(void);
+int lmc_img_pdhg_dual(int dtype, int32_t ny, int32_t nx, double mu, double g_sigma, int isotropic, const void* d_x,
+                      void* d_Ax, void* d_y, double* d_resid, void* d_workspace, size_t workspace_bytes, void* stream);
+int lmc_img_pdhg_primal_resid(int dtype, int32_t ny, int32_t nx, double tau, const void* d_xold, const void* d_x,
+                              const void* d_y, void* d_ATy, double* d_resid, void* d_workspace,
+                              size_t workspace_bytes, void* stream);
+
 /* Per-sample metrics on the device, replacing the reference's per-iteration host callback
  * (prox_lmc_deconv.py:35-36,128-133): for each of the M images of d_x (M,P) -- e.g. the (C,N,P) samples of a
  * run, images_per_chain = N -- d_out (M,4) doubles receives

@@ -123,6 +123,12 @@ SIGNATURES = {
                                C.c_void_p]),
     "lmc_img_tv_prox": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_int32, C.c_double, C.c_int64,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lmc_img_pdhg_workspace_bytes": (C.c_size_t, []),
+    "lmc_img_pdhg_dual": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_int, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lmc_img_pdhg_primal_resid": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                            C.c_void_p]),
     "lmc_img_proxdual": (C.c_int, [C.c_int, C.c_int, C.c_double, C.c_int64, C.c_void_p, C.c_void_p]),
     "lmc_img_l2_prox": (C.c_int, [C.POINTER(ImgProblem), C.c_int, C.c_double, C.c_int32, C.c_double, C.c_double,
                                   C.c_double, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -219,3 +219,12 @@ class L2(ProxOperator):
         if self.warm:
             self.x0 = out
         return out
+
+
+# pyproximal.optimization.primaldual.AdaptivePrimalDual (MAP branch of the driver, prox_lmc_deconv.py:138-445)
+import types as _types
+
+from . import primaldual as _primaldual
+
+optimization = _types.SimpleNamespace(primaldual=_types.SimpleNamespace(
+    AdaptivePrimalDual=_primaldual.AdaptivePrimalDual))

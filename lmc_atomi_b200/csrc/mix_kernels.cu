@@ -12,7 +12,10 @@
 // The target is evaluated in the log2 domain with a max-shift (log-sum-exp), which
 // is algebraically identical to the reference's plain ratio -grad p / p
 // (lmc.py:60-61) but cannot underflow in fp32.
+#include <stdlib.h>
+
 #include "lmc_common.cuh"
+#include "lmc_f2.cuh"
 
 namespace {
 
@@ -223,6 +226,7 @@ __device__ __forceinline__ void drift_centre(const MixP<real>& P, real t0, real 
 template <typename real, int TARGET, int ALG, int NC>
 __device__ __forceinline__ void step_unadjusted(const MixP<real>& P, real& t0, real& t1, real x0, real x1) {
   using M = Math<real>;
+  using L = Lanes<real>;
   Eval<real> e;
   if (ALG == LMC_PGLD) {  // prox_lmc.py:106
     t0 = lmc_soft(t0, P.pr_thr);
@@ -287,16 +291,16 @@ __device__ __forceinline__ void step_unadjusted(const MixP<real>& P, real& t0, r
         real rt = M::sqrt(M::fma(t0, t0, P.sg0 * P.sg0));
         real as = mirror_asinh(t0, rt, P.isg0);
         real lo = P.sg0 * M::sinh(as - thr), hi = P.sg0 * M::sinh(as + thr);
-        real p = (t0 > P.sg0 * sh) ? lo : (rt - P.sg0);
-        p = (t0 < -P.sg0 * sh) ? hi : p;
+        real p = L::select(L::gt(t0, P.sg0 * sh), lo, rt - P.sg0);
+        p = L::select(L::lt(t0, -(P.sg0 * sh)), hi, p);
         e0 -= P.gamma * (M::div(P.inv_lamda, rt) * (t0 - p));
       }
       {
         real rt = M::sqrt(M::fma(t1, t1, P.sg1 * P.sg1));
         real as = mirror_asinh(t1, rt, P.isg1);
         real lo = P.sg1 * M::sinh(as - thr), hi = P.sg1 * M::sinh(as + thr);
-        real p = (t1 > P.sg1 * sh) ? lo : (rt - P.sg1);
-        p = (t1 < -P.sg1 * sh) ? hi : p;
+        real p = L::select(L::gt(t1, P.sg1 * sh), lo, rt - P.sg1);
+        p = L::select(L::lt(t1, -(P.sg1 * sh)), hi, p);
         e1 -= P.gamma * (M::div(P.inv_lamda, rt) * (t1 - p));
       }
     }
@@ -331,19 +335,21 @@ __device__ __forceinline__ real mh_logdens2(const MixP<real>& P, real t0, real t
 template <typename real, int TARGET, int ALG, int NC>
 struct Chain {
   using M = Math<real>;
+  using L = Lanes<real>;
+  using mask = typename L::mask;
   static constexpr bool ADJ = AlgTraits<ALG>::adjusted;
   real t0, t1;
   real cc0, cc1, clog;   // MH chains: proposal centre and log2-density at the current state
-  uint32_t nacc;
+  typename L::count nacc;
   real b_n, b_s0, b_s1, b_s00, b_s01, b_s11;        // fp32/fp64 partial sums of <= 32 steps
-  double m_n, m_s0, m_s1, m_s00, m_s01, m_s11;      // fp64 totals
+  typename L::dbl m_n, m_s0, m_s1, m_s00, m_s01, m_s11;      // fp64 totals (per lane)
 
   __device__ __forceinline__ void init(const MixP<real>& P, real a0, real a1) {
     t0 = a0; t1 = a1;
-    cc0 = cc1 = clog = 0;
-    nacc = 0;
-    b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = 0;
-    m_n = m_s0 = m_s1 = m_s00 = m_s01 = m_s11 = 0;
+    cc0 = cc1 = clog = real(0);
+    nacc = typename L::count{};
+    b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = real(0);
+    m_n = m_s0 = m_s1 = m_s00 = m_s01 = m_s11 = L::dbl_set(0.0);
     if (ADJ) {
       Eval<real> cur;
       eval_target<real, TARGET, NC, false>(P, t0, t1, cur);
@@ -353,10 +359,10 @@ struct Chain {
   }
 
   // one transition; returns whether a sample was emitted (always, for unadjusted samplers)
-  __device__ __forceinline__ bool step(const MixP<real>& P, real x0, real x1, real u) {
+  __device__ __forceinline__ mask step(const MixP<real>& P, real x0, real x1, real u) {
     if (!ADJ) {
       step_unadjusted<real, TARGET, ALG, NC>(P, t0, t1, x0, x1);
-      return true;
+      return L::not_(L::gt(real(0), real(0)));   // all lanes emit
     }
     // lmc.py:124-130: propose, MH ratio p(new) q(old|new) / (p(old) q(new|old)),
     // accept iff u <= min(1, ratio); a NaN ratio accepts (Python's min(1, nan) == 1).
@@ -371,18 +377,20 @@ struct Chain {
     real lq = (M::fma(r0, r0, r1 * r1) - M::fma(f0, f0, f1 * f1)) * P.inv4g;  // natural log
     real lr2 = (plog - clog) + real(1.4426950408889634) * lq;
     real ratio = M::exp2(lr2);
-    bool emitted = !(u > M::min(real(1), ratio));
-    if (emitted) {
-      t0 = n0; t1 = n1; cc0 = pc0; cc1 = pc1; clog = plog;
-      ++nacc;
-    }
+    const mask emitted = L::not_(L::gt(u, M::min(real(1), ratio)));
+    t0 = L::select(emitted, n0, t0);
+    t1 = L::select(emitted, n1, t1);
+    cc0 = L::select(emitted, pc0, cc0);
+    cc1 = L::select(emitted, pc1, cc1);
+    clog = L::select(emitted, plog, clog);
+    L::count_add(nacc, emitted);
     return emitted;
   }
 
   // running sums over the emitted samples
-  __device__ __forceinline__ void accumulate(bool emitted) {
+  __device__ __forceinline__ void accumulate(mask emitted) {
     if (ADJ) {
-      real f = emitted ? real(1) : real(0);
+      real f = L::select(emitted, real(1), real(0));
       b_n += f;
       b_s0 = M::fma(f, t0, b_s0);
       b_s1 = M::fma(f, t1, b_s1);
@@ -399,8 +407,9 @@ struct Chain {
   }
 
   __device__ __forceinline__ void flush() {
-    m_n += b_n; m_s0 += b_s0; m_s1 += b_s1; m_s00 += b_s00; m_s01 += b_s01; m_s11 += b_s11;
-    b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = 0;
+    L::dbl_add(m_n, b_n); L::dbl_add(m_s0, b_s0); L::dbl_add(m_s1, b_s1);
+    L::dbl_add(m_s00, b_s00); L::dbl_add(m_s01, b_s01); L::dbl_add(m_s11, b_s11);
+    b_n = b_s0 = b_s1 = b_s00 = b_s01 = b_s11 = real(0);
   }
 };
 
@@ -411,37 +420,49 @@ __device__ __forceinline__ void hist_add(const MixIo& io, double a0, double a1) 
     atomicAdd(&io.hist[ix * io.hist_bins + iy], 1ull);
 }
 
+// histogram of the emitted, live lanes of a thread's state
+template <typename real>
+__device__ __forceinline__ void hist_lanes(const MixIo& io, real t0, real t1, typename Lanes<real>::mask emitted,
+                                           typename Lanes<real>::mask live) {
+  if constexpr (Lanes<real>::N == 2) {
+    if (emitted.x && live.x) hist_add(io, (double)t0.x, (double)t1.x);
+    if (emitted.y && live.y) hist_add(io, (double)t0.y, (double)t1.y);
+  } else {
+    if (emitted && live) hist_add(io, (double)t0, (double)t1);
+  }
+}
+
 // Production loop over steps [kb, ke): Philox noise, registers only.  STATS = accumulate
 // moments (steps past the burn-in), HIST = bin every io.hist_every-th emitted step.
 // Unadjusted samplers use one Philox block per TWO steps (words x,y for even k, z,w for odd
 // k, block counter k >> 1); adjusted samplers one block per step (x,y normals, z uniform).
 template <typename real, int TARGET, int ALG, int NC, bool STATS, bool HIST>
 __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch, const MixP<real>& P,
-                                               const MixIo& io, uint32_t c_lo, uint32_t c_hi, bool live,
-                                               long long kb, long long ke) {
+                                               const MixIo& io, typename Lanes<real>::cid cid,
+                                               typename Lanes<real>::mask live, long long kb, long long ke) {
   using M = Math<real>;
+  using L = Lanes<real>;
   constexpr bool ADJ = AlgTraits<ALG>::adjusted;
   long long hcount = 0;
   if (HIST) hcount = io.hist_every - (kb % io.hist_every);
-  auto after = [&](bool emitted) {
+  auto after = [&](typename L::mask emitted) {
     if (STATS) ch.accumulate(emitted);
     if (HIST) {
       if (--hcount == 0) {
         hcount = io.hist_every;
-        if (emitted && live) hist_add(io, (double)ch.t0, (double)ch.t1);
+        hist_lanes<real>(io, ch.t0, ch.t1, emitted, live);
       }
     }
   };
   auto block = [&](long long ctr) {
-    return lmc_philox4x32_10_rk(make_uint4((uint32_t)ctr, LMC_STREAM_STEP | ((uint32_t)(ctr >> 32) << 8), c_lo, c_hi),
-                                io.rk);
+    return L::philox((uint32_t)ctr, LMC_STREAM_STEP | ((uint32_t)(ctr >> 32) << 8), cid, io.rk);
   };
   long long k = kb;
   if (ADJ) {
     while (k < ke) {
       const int n = (int)((ke - k) < 32 ? (ke - k) : 32);
       for (int j = 0; j < n; ++j) {
-        uint4 r = block(k + j);
+        auto r = block(k + j);
         real x0, x1;
         M::normals(r.x, r.y, x0, x1);
         after(ch.step(P, x0, x1, M::uniform(r.z)));
@@ -452,7 +473,7 @@ __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch,
     return;
   }
   if ((k & 1) && k < ke) {   // odd start (odd burn-in): second half of block k >> 1
-    uint4 r = block(k >> 1);
+    auto r = block(k >> 1);
     real x0, x1;
     M::normals(r.z, r.w, x0, x1);
     after(ch.step(P, x0, x1, real(0)));
@@ -463,7 +484,7 @@ __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch,
     const int n = (int)(left < 16 ? left : 16);
     const long long c0 = k >> 1;
     for (int j = 0; j < n; ++j) {
-      uint4 r = block(c0 + j);
+      auto r = block(c0 + j);
       real x0, x1;
       M::normals(r.x, r.y, x0, x1);
       after(ch.step(P, x0, x1, real(0)));
@@ -474,7 +495,7 @@ __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch,
     k += 2 * n;
   }
   if (k < ke) {
-    uint4 r = block(k >> 1);
+    auto r = block(k >> 1);
     real x0, x1;
     M::normals(r.x, r.y, x0, x1);
     after(ch.step(P, x0, x1, real(0)));
@@ -482,17 +503,26 @@ __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch,
   if (STATS) ch.flush();
 }
 
+template <typename real> struct ScalarOf { using type = real; };
+template <> struct ScalarOf<f2> { using type = float; };
+
 // Occupancy experiment (r01e, K=20000, 2^20 chains, fp32 production chains): a minimum of 5 resident CTAs per SM
 // (48 registers) gave 167.9, 6 (40 registers, spills) 164.1, and even the hint "4" (which only changes the
 // register allocator's target) 165.8 against 170.8 G chain-steps/s without any hint: the chains are bound by the
 // MUFU/FMA pipes (math-pipe throttle + fixed-latency waits), not by occupancy.  No hint.
+//
+// real = f2 (production fp32): every thread advances TWO chains, lanes x / y of the packed type, chains
+// item*64 + lane and item*64 + 32 + lane (both halves of a warp's loads and stores stay coalesced).
 template <typename real, int TARGET, int ALG, int NC, bool PROD>
 __global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant__ MixP<real> P,
                                                           const __grid_constant__ MixIo io) {
   using M = Math<real>;
+  using L = Lanes<real>;
+  using sreal = typename ScalarOf<real>::type;
   constexpr bool ADJ = AlgTraits<ALG>::adjusted;
+  constexpr int PER_ITEM = 32 * L::N;
   const int lane = threadIdx.x & 31;
-  real* theta = (real*)io.theta;
+  sreal* theta = (sreal*)io.theta;
   const long long K = io.K;
 
   for (;;) {
@@ -500,34 +530,49 @@ __global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant_
     if (lane == 0) item = atomicAdd(io.queue, 1u);
     item = __shfl_sync(0xffffffffu, item, 0);
     if (item >= (unsigned)io.n_items) break;
-    const long long c = (long long)item * 32 + lane;
-    const bool live = c < io.C;
-    const unsigned long long gc = io.chain_offset + (unsigned long long)(live ? c : 0);
-    const uint32_t c_lo = (uint32_t)gc, c_hi = (uint32_t)(gc >> 32);
-
-    real a0 = 0, a1 = 0;
+    const long long c = (long long)item * PER_ITEM + lane;
+    typename L::mask live;
+    typename L::cid cid;
+    real a0 = real(0), a1 = real(0);
+    if constexpr (L::N == 2) {
+      const long long cy = c + 32;
+      live = b2{c < io.C, cy < io.C};
+      const unsigned long long gx = io.chain_offset + (unsigned long long)(live.x ? c : 0);
+      const unsigned long long gy = io.chain_offset + (unsigned long long)(live.y ? cy : 0);
+      cid = typename L::cid{(uint32_t)gx, (uint32_t)(gx >> 32), (uint32_t)gy, (uint32_t)(gy >> 32)};
+      if (!io.init_from_rng) {
+        if (live.x) { a0.x = theta[2 * c]; a1.x = theta[2 * c + 1]; }
+        if (live.y) { a0.y = theta[2 * cy]; a1.y = theta[2 * cy + 1]; }
+      }
+    } else {
+      live = c < io.C;
+      const unsigned long long gc = io.chain_offset + (unsigned long long)(live ? c : 0);
+      cid = typename L::cid{(uint32_t)gc, (uint32_t)(gc >> 32)};
+      if (!io.init_from_rng && live) {
+        a0 = theta[2 * c];
+        a1 = theta[2 * c + 1];
+      }
+    }
     if (io.init_from_rng) {
-      uint4 r = lmc_philox4x32_10_rk(make_uint4(0u, LMC_STREAM_INIT, c_lo, c_hi), io.rk);
+      auto r = L::philox(0u, LMC_STREAM_INIT, cid, io.rk);
       M::normals(r.x, r.y, a0, a1);
-    } else if (live) {
-      a0 = theta[2 * c];
-      a1 = theta[2 * c + 1];
     }
     Chain<real, TARGET, ALG, NC> ch;
     ch.init(P, a0, a1);
 
-    if (PROD) {
+    if constexpr (PROD) {
       const long long kb = io.burnin < K ? (io.burnin > 0 ? io.burnin : 0) : K;
       const bool hist = io.hist != nullptr && io.hist_every > 0;
-      run_production<real, TARGET, ALG, NC, false, false>(ch, P, io, c_lo, c_hi, live, 0, kb);
-      if (hist) run_production<real, TARGET, ALG, NC, true, true>(ch, P, io, c_lo, c_hi, live, kb, K);
-      else run_production<real, TARGET, ALG, NC, true, false>(ch, P, io, c_lo, c_hi, live, kb, K);
+      run_production<real, TARGET, ALG, NC, false, false>(ch, P, io, cid, live, 0, kb);
+      if (hist) run_production<real, TARGET, ALG, NC, true, true>(ch, P, io, cid, live, kb, K);
+      else run_production<real, TARGET, ALG, NC, true, false>(ch, P, io, cid, live, kb, K);
     } else {
-      // validation mode: the reference's own draws come from HBM, every state goes back
+      // validation mode (one chain per thread): the reference's own draws come from HBM, every state goes back
+      static_assert(PROD || L::N == 1, "validation mode runs one chain per thread");
       const real* noise = (const real*)io.noise;
       const real* unif = (const real*)io.unif;
       real* traj = (real*)io.traj;
-      uint4 rnd = make_uint4(0, 0, 0, 0);
+      typename L::blk rnd{};
       for (long long k = 0; k < K; ++k) {
         real x0, x1, u = 0;
         if (noise != nullptr) {
@@ -535,12 +580,12 @@ __global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant_
           x1 = live ? noise[(c * K + k) * 2 + 1] : real(0);
           if (ADJ) u = live ? unif[c * K + k] : real(0);
         } else if (ADJ) {
-          rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), io.rk);
+          rnd = L::philox((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), cid, io.rk);
           M::normals(rnd.x, rnd.y, x0, x1);
           u = M::uniform(rnd.z);
         } else if ((k & 1) == 0) {
           long long kb = k >> 1;
-          rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), io.rk);
+          rnd = L::philox((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), cid, io.rk);
           M::normals(rnd.x, rnd.y, x0, x1);
         } else {
           M::normals(rnd.z, rnd.w, x0, x1);
@@ -562,15 +607,30 @@ __global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant_
     }
 
     // unadjusted samplers emit every step: the count is known without a per-step add
-    if (!ADJ) ch.m_n = (double)(K - (io.burnin < K ? (io.burnin > 0 ? io.burnin : 0) : K));
-    double m_n = ch.m_n, m_s0 = ch.m_s0, m_s1 = ch.m_s1, m_s00 = ch.m_s00, m_s01 = ch.m_s01, m_s11 = ch.m_s11;
-    if (live) {
-      theta[2 * c] = ch.t0;
-      theta[2 * c + 1] = ch.t1;
-      if (io.naccept != nullptr) io.naccept[c] = ADJ ? ch.nacc : (uint32_t)K;
-      if (io.hist != nullptr && io.hist_every == 0) hist_add(io, (double)ch.t0, (double)ch.t1);
+    if (!ADJ) ch.m_n = L::dbl_set((double)(K - (io.burnin < K ? (io.burnin > 0 ? io.burnin : 0) : K)));
+    double m_n = L::dbl_total(ch.m_n, live), m_s0 = L::dbl_total(ch.m_s0, live), m_s1 = L::dbl_total(ch.m_s1, live);
+    double m_s00 = L::dbl_total(ch.m_s00, live), m_s01 = L::dbl_total(ch.m_s01, live),
+           m_s11 = L::dbl_total(ch.m_s11, live);
+    if constexpr (L::N == 2) {
+      const long long cy = c + 32;
+      if (live.x) {
+        theta[2 * c] = ch.t0.x;
+        theta[2 * c + 1] = ch.t1.x;
+        if (io.naccept != nullptr) io.naccept[c] = ADJ ? ch.nacc.x : (uint32_t)K;
+      }
+      if (live.y) {
+        theta[2 * cy] = ch.t0.y;
+        theta[2 * cy + 1] = ch.t1.y;
+        if (io.naccept != nullptr) io.naccept[cy] = ADJ ? ch.nacc.y : (uint32_t)K;
+      }
+      if (io.hist != nullptr && io.hist_every == 0) hist_lanes<real>(io, ch.t0, ch.t1, b2{true, true}, live);
     } else {
-      m_n = m_s0 = m_s1 = m_s00 = m_s01 = m_s11 = 0;
+      if (live) {
+        theta[2 * c] = ch.t0;
+        theta[2 * c + 1] = ch.t1;
+        if (io.naccept != nullptr) io.naccept[c] = ADJ ? ch.nacc : (uint32_t)K;
+        if (io.hist != nullptr && io.hist_every == 0) hist_add(io, (double)ch.t0, (double)ch.t1);
+      }
     }
     m_n = lmc_warp_sum(m_n); m_s0 = lmc_warp_sum(m_s0); m_s1 = lmc_warp_sum(m_s1);
     m_s00 = lmc_warp_sum(m_s00); m_s01 = lmc_warp_sum(m_s01); m_s11 = lmc_warp_sum(m_s11);
@@ -694,10 +754,33 @@ int launch_one(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
   return 0;
 }
 
+// production = nothing but registers inside the K-loop (Philox noise, no per-step outputs)
+inline bool is_production(const MixIo& io) { return io.noise == nullptr && io.traj == nullptr && io.accept == nullptr; }
+
+// LMC_MIX_SCALAR=1 keeps fp32 production chains on the one-chain-per-thread kernel (A/B runs of the packed path)
+inline bool packed_enabled();
+inline long long items_for(int dtype, const MixIo& io, long long C) {
+  const bool packed = dtype == LMC_F32 && is_production(io) && packed_enabled();
+  return packed ? (C + 63) / 64 : (C + 31) / 32;
+}
+inline bool packed_enabled() {
+  const char* e = getenv("LMC_MIX_SCALAR");
+  return !(e != nullptr && e[0] == '1');
+}
+
 template <typename real, int TARGET, int ALG>
-int launch_nc(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
-  // production = nothing but registers inside the K-loop (Philox noise, no per-step outputs)
-  const bool prod = io.noise == nullptr && io.traj == nullptr && io.accept == nullptr;
+int launch_nc(const lmc_mix_target& T, const lmc_mix_step& S, MixIo io, cudaStream_t st) {
+  const bool prod = is_production(io);
+  if constexpr (sizeof(real) == 4) {
+    if (prod && packed_enabled()) {   // fp32 production: two chains per thread, packed FP32 instructions
+      MixP<f2> P2;
+      fill_params(T, S, P2);
+      // io.n_items was sized for 64 chains per warp by lmc_mix_run (items_for)
+      return P2.n == 5 ? launch_one<f2, TARGET, ALG, 5, true>(P2, io, st) : launch_one<f2, TARGET, ALG, 0, true>(P2, io, st);
+    }
+  }
+  MixP<real> P;
+  fill_params(T, S, P);
   if (P.n == 5) return prod ? launch_one<real, TARGET, ALG, 5, true>(P, io, st)
                             : launch_one<real, TARGET, ALG, 5, false>(P, io, st);
   return prod ? launch_one<real, TARGET, ALG, 0, true>(P, io, st) : launch_one<real, TARGET, ALG, 0, false>(P, io, st);
@@ -705,10 +788,8 @@ int launch_nc(const MixP<real>& P, const MixIo& io, cudaStream_t st) {
 
 template <typename real>
 int dispatch(const lmc_mix_target& T, const lmc_mix_step& S, const MixIo& io, cudaStream_t st) {
-  MixP<real> P;
-  fill_params(T, S, P);
 #define LMC_CASE(TG, AL) \
-  if (T.kind == TG && S.alg == AL) return launch_nc<real, TG, AL>(P, io, st);
+  if (T.kind == TG && S.alg == AL) return launch_nc<real, TG, AL>(T, S, io, st);
   LMC_CASE(LMC_TARGET_GAUSS, LMC_ULA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_MALA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_PULA)
@@ -747,7 +828,7 @@ extern "C" int lmc_mix_run(const lmc_mix_target* target, const lmc_mix_step* ste
   LMC_REQUIRE(target->n >= 1 && target->n <= LMC_MAX_COMP, "lmc_mix_run: n=%d outside 1..%d", target->n,
               LMC_MAX_COMP);
   LMC_REQUIRE(C >= 0 && K >= 0, "lmc_mix_run: negative C or K");
-  LMC_REQUIRE(C < ((int64_t)1 << 36), "lmc_mix_run: C too large");
+  LMC_REQUIRE(C <= ((int64_t)1 << 36) - 64, "lmc_mix_run: C too large (work items are 32-bit)");
   LMC_REQUIRE(step->gamma > 0, "lmc_mix_run: gamma must be positive");
   if (C == 0) return 0;
   LMC_REQUIRE(uio->d_theta != nullptr, "lmc_mix_run: d_theta is required");
@@ -787,7 +868,7 @@ extern "C" int lmc_mix_run(const lmc_mix_target* target, const lmc_mix_step* ste
   io.hist_bins = uio->hist_bins;
   io.hist_lo = uio->hist_lo;
   io.hist_scale = uio->d_hist ? uio->hist_bins / (uio->hist_hi - uio->hist_lo) : 0.0;
-  io.n_items = (int)((C + 31) / 32);
+  io.n_items = (int)items_for(dtype, io, C);
 
   LMC_CUDA_OK(cudaMemsetAsync(io.queue, 0, 256, st));
   int rc = dtype == LMC_F64 ? dispatch<double>(*target, *step, io, st) : dispatch<float>(*target, *step, io, st);

@@ -4,8 +4,9 @@ Builds the operators exactly as the driver does (prox_lmc_deconv.py:52-125: H5/H
 y = H5 img + N(0, sigma^2) from ``default_rng(seed)``, L2 / MC-TV / ME-TV data terms, TV / L21 / L1 priors) and
 runs the nine sampling experiments (:447-703) on the CUDA path: ULPDA or MYULA for blur sizes 5, 6, 7 and data
 terms L2, MC-TV, ME-TV.  The per-iteration host callback of the driver (:128-133) is replaced by
-``algs.DeviceMetrics`` (the samples never leave the GPU except for the returned posterior mean); plotting and
-the MAP branch (PDHG, :138-445) are outside the sampler hot path."""
+``algs.DeviceMetrics`` (the samples never leave the GPU except for the returned posterior mean).
+``compute_MAP=True`` runs the driver's other branch (:138-445): adaptive PDHG MAP estimates of the same nine models
+(``primaldual.AdaptivePrimalDual``).  Plotting is out of scope."""
 from __future__ import annotations
 
 import os
@@ -13,7 +14,7 @@ import os
 import numpy as np
 from numpy.random import default_rng
 
-from . import algs, compat, deconv_bench
+from . import algs, compat, deconv_bench, primaldual
 
 MODELS = tuple((k, term) for term in ("l2", "mc", "me") for k in (5, 6, 7))   # order of prox_lmc_deconv.py:447-703
 
@@ -40,10 +41,7 @@ def prox_lmc_deconv(gamma_mc=15., gamma_me=15., sigma=0.75, tau=0.3, N=1000, nit
     ``default_rng(seed)``, algs.py:431,561, so all nine models see the same stream; passing it once, e.g. as a
     device tensor, avoids drawing it nine times).  Returns a dict: per model the posterior mean, the per-sample
     metric curves of the driver's callback (:128-133) and the PSNR of the mean (:707-735)."""
-    if compute_MAP:
-        raise NotImplementedError("the MAP branch (PDHG, prox_lmc_deconv.py:138-445) is an optimiser outside the "
-                                  "sampler hot path; there is no CUDA path for it")
-    if alg not in ("ULPDA", "MYULA"):
+    if not compute_MAP and alg not in ("ULPDA", "MYULA"):
         raise ValueError("alg must be 'ULPDA' or 'MYULA'")
     img = load_image(image)
     ny, nx = img.shape
@@ -68,10 +66,18 @@ def prox_lmc_deconv(gamma_mc=15., gamma_me=15., sigma=0.75, tau=0.3, N=1000, nit
     l1iso, l1 = compat.L21(ndim=2, sigma=tau), compat.L1(sigma=tau)            # :116,119
     tv = compat.TV(dims=(ny, nx), sigma=tau, niter=niter_tv)                   # :122
     x0 = np.zeros(ny * nx)
-    out = {"image": img, "observation": y.reshape(ny, nx), "alg": alg, "models": {}}
+    out = {"image": img, "observation": y.reshape(ny, nx), "alg": "MAP" if compute_MAP else alg, "models": {}}
     for k, term in models:
         f = data_term(k, term)
         dm = algs.DeviceMetrics(img.ravel())
+        if compute_MAP:     # :138-445: adaptive PDHG, the driver's `if compute_MAP: ... else: <samplers>`
+            g = l1 if term == "mc" else l1iso
+            xmap, _ = primaldual.AdaptivePrimalDual(f, g, Gop, tau=tau0, mu=mu0, x0=x0, niter=niter_MAP, dtype=dtype,
+                                                    device_metrics=dm)
+            out["models"][f"{term}_{k}"] = {
+                "map": xmap.reshape(ny, nx), "cost_l2_plus_g": dm.cost, "err": dm.err, "snr": dm.snr, "psnr": dm.psnr,
+                "mse": dm.mse, "map_psnr": float(10 * np.log10(255. ** 2 / np.mean((xmap - img.ravel()) ** 2)))}
+            continue
         if alg == "ULPDA":
             g = l1 if term == "mc" else l1iso          # the driver pairs MC-TV with the anisotropic prior (:542)
             s = algs.UnadjustedLangevinPrimalDual(f, g, Gop, tau=tau0, mu=mu0, theta=1., x0=x0, gfirst=False,

@@ -108,3 +108,18 @@ def test_ulpda_m1_matches_reference_figure(einstein, curves):
                                                        psnr.append(D.psnr(xt, x)), mse.append(D.mse(xt, x))))
     worst = _compare(curves, "einstein_ULPDA", 1, snr, psnr, mse, n)
     print("ULPDA M1 worst |diff|:", worst)
+
+
+def test_map_m1_matches_reference_figure(einstein, curves):
+    """Pins the MAP branch (pyproximal AdaptivePrimalDual, prox_lmc_deconv.py:138-153): l2 residual norms and the
+    (alpha, eta, s, delta) = (0.5, 0.95, 1, 1.5) adaptation, through the first step-size changes."""
+    n = 13
+    pb = D.build_problem(einstein)
+    xt = einstein.ravel()
+    snr, psnr, mse = [], [], []
+    _, steps = D.AdaptivePrimalDual(pb["l2"](), pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], niter=n,
+                                    callback=lambda x: (snr.append(D.signal_noise_ratio(xt, x)),
+                                                        psnr.append(D.psnr(xt, x)), mse.append(D.mse(xt, x))))
+    assert len({round(t, 12) for t, _, _ in steps}) > 1          # the step size did adapt inside the window
+    worst = _compare(curves, "einstein_MAP", 1, snr, psnr, mse, n)
+    print("MAP M1 worst |diff|:", worst)

@@ -73,3 +73,19 @@ def test_einstein_run_matches_reference_figures(torch, einstein, noise, alg):
                    "mean_psnr": {k: v["mean_psnr"] for k, v in res["models"].items()}}, f, indent=1)
     bad = {k: v for k, v in worst.items() if not v < DB_TOL}
     assert not bad, bad
+
+
+def test_einstein_map_matches_reference_figure(torch, einstein):
+    """MAP branch (expt_deconv.sh:4: --compute_MAP=True --niter_MAP=1000): adaptive PDHG on the CUDA operators against
+    fig_prox_lmc_deconv_einstein_MAP_1000_snr_psnr_mse for all nine models."""
+    from lmc_atomi_b200.prox_lmc_deconv import prox_lmc_deconv
+    curves = np.load(os.path.join(GOLDEN, "deconv_curves.npz"))
+    res = prox_lmc_deconv(gamma_mc=15., gamma_me=15., sigma=0.75, tau=0.3, niter_MAP=N, image=einstein,
+                          compute_MAP=True, seed=0, dtype="float64")
+    worst = residuals(curves, "einstein_MAP", res)
+    os.makedirs("gpurun_out", exist_ok=True)
+    with open("gpurun_out/pinned_MAP.json", "w") as f:
+        json.dump({"worst_abs_diff_db": worst,
+                   "map_psnr": {k: v["map_psnr"] for k, v in res["models"].items()}}, f, indent=1)
+    bad = {k: v for k, v in worst.items() if not v < DB_TOL}
+    assert not bad, bad
