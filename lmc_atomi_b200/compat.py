@@ -228,3 +228,103 @@ from . import primaldual as _primaldual
 
 optimization = _types.SimpleNamespace(primaldual=_types.SimpleNamespace(
     AdaptivePrimalDual=_primaldual.AdaptivePrimalDual))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Running the reference's own driver unchanged: `prox_lmc_deconv.py` does `import pylops, pyproximal, algs` plus
+# skimage / fire / plotting imports (prox_lmc_deconv.py:4-32).  install() registers this package's stand-ins under
+# those names, so `python -c "from lmc_atomi_b200 import compat; compat.install(); import prox_lmc_deconv"` binds the
+# unmodified driver to the CUDA path.  Plot / CLI libraries become inert (their calls do nothing).
+def _skimage_modules():
+    """skimage.io.imread / data.camera / metrics.{peak_signal_noise_ratio, mean_squared_error} as the driver uses
+    them (prox_lmc_deconv.py:25-27, 45-48, 128-133)."""
+    sk = _types.ModuleType("skimage")
+
+    def imread(path):
+        from PIL import Image
+        return np.asarray(Image.open(path))
+
+    def camera():
+        raise NotImplementedError("skimage.data.camera() (the 512x512 cameraman image) is not available offline; "
+                                  "use --image=einstein")
+
+    def mean_squared_error(a, b):
+        return float(np.mean((np.asarray(a, dtype=np.float64) - np.asarray(b, dtype=np.float64)) ** 2))
+
+    def peak_signal_noise_ratio(image_true, image_test, data_range=None):
+        if data_range is None:       # skimage: the dtype range of image_true (uint8 -> 255) when it is non-negative
+            t = np.asarray(image_true)
+            data_range = 255. if t.dtype == np.uint8 else float(t.max() - t.min())
+        return float(10 * np.log10(data_range ** 2 / mean_squared_error(image_true, image_test)))
+
+    sk.io = _types.ModuleType("skimage.io")
+    sk.io.imread = imread
+    sk.data = _types.ModuleType("skimage.data")
+    sk.data.camera = camera
+    sk.metrics = _types.ModuleType("skimage.metrics")
+    sk.metrics.peak_signal_noise_ratio = peak_signal_noise_ratio
+    sk.metrics.mean_squared_error = mean_squared_error
+    return {"skimage": sk, "skimage.io": sk.io, "skimage.data": sk.data, "skimage.metrics": sk.metrics}
+
+
+class _InertModule(_types.ModuleType):
+    """fire / matplotlib / seaborn / scienceplots / fastprogress: every attribute is a do-nothing callable."""
+
+    class _Obj:
+        def __call__(self, *a, **k):
+            return _InertModule._Obj()
+
+        def __getattr__(self, name):
+            if name.startswith("__"):
+                raise AttributeError(name)
+            return _InertModule._Obj()
+
+        def __getitem__(self, k):
+            return _InertModule._Obj()
+
+        def __iter__(self):
+            return iter((_InertModule._Obj(), _InertModule._Obj()))
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+        return _InertModule._Obj()
+
+
+def install(force=False):
+    """Registers `algs`, `pylops`, `pyproximal`, `skimage` (and inert plot / CLI modules) in sys.modules unless the
+    real library is importable (``force`` replaces it anyway).  Returns the list of names it registered."""
+    import importlib
+    import sys
+    from . import algs as _algs
+    this = sys.modules[__name__]
+    pl = _types.ModuleType("pylops")
+    pl.Gradient, pl.Identity = Gradient, Identity
+    pl.signalprocessing = _types.ModuleType("pylops.signalprocessing")
+    pl.signalprocessing.Convolve2D = Convolve2D
+    pp = _types.ModuleType("pyproximal")
+    for name in ("L1", "L2", "L21", "TV", "ProxOperator"):
+        setattr(pp, name, getattr(this, name))
+    pp.optimization = _types.ModuleType("pyproximal.optimization")
+    pp.optimization.primaldual = _types.ModuleType("pyproximal.optimization.primaldual")
+    pp.optimization.primaldual.AdaptivePrimalDual = _primaldual.AdaptivePrimalDual
+    mods = {"algs": _algs, "pylops": pl, "pylops.signalprocessing": pl.signalprocessing, "pyproximal": pp,
+            "pyproximal.optimization": pp.optimization, "pyproximal.optimization.primaldual": pp.optimization.primaldual}
+    mods.update(_skimage_modules())
+    for name in ("fire", "matplotlib", "matplotlib.pyplot", "matplotlib.cm", "seaborn", "scienceplots", "fastprogress"):
+        mods[name] = _InertModule(name)
+    mods["matplotlib"].pyplot, mods["matplotlib"].cm = mods["matplotlib.pyplot"], mods["matplotlib.cm"]
+    done = []
+    for name, mod in mods.items():
+        root = name.split(".")[0]
+        if not force and name != "algs":
+            try:
+                importlib.import_module(root)
+                if not isinstance(sys.modules.get(root), (_InertModule,)) and root not in done and \
+                        sys.modules[root] is not mods.get(root):
+                    continue       # the real library is installed: leave it
+            except ImportError:
+                pass
+        sys.modules[name] = mod
+        done.append(name)
+    return done

@@ -13,18 +13,19 @@ size_t myula_ws_bytes(int ny, int nx, long long C) {
          align_up((size_t)C * P * sizeof(real)) /* grad */ + align_up((size_t)6 * C * P * sizeof(real)) /* duals */;
 }
 
-// the band kernel covers the H5 / H6 / H7 blurs of the driver on images of even width (the TV phases move two
-// columns per thread; the gradient phase does so when the tap windows start on even columns, i.e. H5)
+// the band kernel covers the H5 / H6 / H7 blurs of the driver; two image columns per thread on even widths (the
+// gradient phase when the tap windows also start on the driver's columns), one column per thread on odd widths
+// (the reference's own einstein.png is 667 x 877)
 template <typename real>
 bool myula_band_ok(const lmc_img_problem* pb) {
-  if (pb->ntap_y != pb->ntap_x || pb->ntap_y < 5 || pb->ntap_y > 7 || (pb->nx & 1)) return false;
+  if (pb->ntap_y != pb->ntap_x || pb->ntap_y < 5 || pb->ntap_y > 7) return false;
   return myula_band_smem_bytes<real, 7>(band_pitch(pb->nx)) <= 200 * 1024;
 }
 
-template <typename real, int NT, int GW>
+template <typename real, int NT, int GW, int TW = 2>
 int launch_myula_band(MyulaArgs<real>& A, cudaStream_t st) {
   const size_t smem = myula_band_smem_bytes<real, NT>(A.pitch);
-  auto kern = img_myula_band_kernel<real, NT, GW>;
+  auto kern = img_myula_band_kernel<real, NT, GW, TW>;
   int dev = 0, sms = 0, occ = 0;
   LMC_CUDA_OK(cudaGetDevice(&dev));
   LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -106,6 +107,13 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
   }
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
   if (band) {
+    if (pb->nx & 1) {   // odd width: rows are not pair-aligned, one column per thread in every phase
+      switch (pb->ntap_y) {
+        case 5: return launch_myula_band<real, 5, 1, 1>(A, st);
+        case 6: return launch_myula_band<real, 6, 1, 1>(A, st);
+        default: return launch_myula_band<real, 7, 1, 1>(A, st);
+      }
+    }
     const void* ptrs[] = {A.x, A.b, A.grad, A.D};
     for (const void* p : ptrs)
       LMC_REQUIRE(reinterpret_cast<size_t>(p) % (2 * sizeof(real)) == 0,
@@ -165,8 +173,8 @@ extern "C" int lmc_img_myula_run_band(const lmc_img_problem* pb, const lmc_img_m
   LMC_REQUIRE(pr->tv_niter >= 0 && pr->tv_sigma * pr->epsg * pr->gamma > 0,
               "lmc_img_myula_run_band: TV needs niter >= 0 and sigma*epsg*gamma > 0");
   LMC_REQUIRE(lmc_img_myula_band_supported(pb, dtype),
-              "lmc_img_myula_run_band: needs 5/6/7 blur taps on both axes, an even width and a row that fits in "
-              "shared memory (use lmc_img_myula_run)");
+              "lmc_img_myula_run_band: needs 5/6/7 blur taps on both axes and a row that fits in shared memory "
+              "(use lmc_img_myula_run)");
   if (C == 0 || N == 0) return 0;
   LMC_REQUIRE(io->d_x != nullptr && pb->d_b != nullptr, "lmc_img_myula_run_band: d_x and d_b are required");
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,

@@ -14,7 +14,6 @@ namespace {
 
 constexpr int MB_RB = 16;   // rows per band = per objective partial
 constexpr int MB_HB = 8;    // rows per TV sub-band
-constexpr int MB_W = 2;     // image columns per thread
 
 template <typename real, int NT>
 __host__ __device__ inline size_t myula_band_smem_bytes(int pitch) {
@@ -24,9 +23,10 @@ __host__ __device__ inline size_t myula_band_smem_bytes(int pitch) {
 
 // rr = p_it + c (p_it - p_{it-1}) (both components) on image rows [r_first, r_first + nrows), all columns;
 // zero outside the image (pad columns are never written and stay zero)
-template <typename real>
+template <typename real, int TW>
 __device__ __forceinline__ void mband_stage_rr(const MyulaArgs<real>& A, long long chain, int it, int r_first, int nrows,
                                                real* RR, real* SS) {
+  constexpr int MB_W = TW;   // image columns per thread of the TV phases (2; 1 for odd widths)
   using P2 = Pack<real, MB_W>;
   const Geom<real>& g = A.g;
   const int pitch = A.pitch;
@@ -78,7 +78,7 @@ __device__ __forceinline__ void mband_stage_rr(const MyulaArgs<real>& A, long lo
 }
 
 // sol = x - gamma div(rr, ss) for columns [col, col + W) of local row a (RR/SS row a = image row, row a-1 above)
-template <typename real>
+template <typename real, int MB_W>
 __device__ __forceinline__ Pack<real, MB_W> mband_sol(const real* RR, const real* SS, int pitch, int a, int col,
                                                       const Pack<real, MB_W>& xv, real gamma) {
   using P2 = Pack<real, MB_W>;
@@ -165,8 +165,9 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
 }
 
 // ---------------------------------------------------------------- phase T_it
-template <typename real>
+template <typename real, int TW>
 __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int it, real* smem, double* red) {
+  constexpr int MB_W = TW;
   using P2 = Pack<real, MB_W>;
   constexpr int RB = MB_RB, HB = MB_HB;
   const Geom<real>& g = A.g;
@@ -195,7 +196,7 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
       P2 xr[HB + 1];
       if (col0 < g.nx) load_x(col0, xr);
       if (r0 != i0) __syncthreads();   // the previous sub-band's readers are done
-      mband_stage_rr(A, chain, it, r0 - 1, HB + 2, RR, SS);
+      mband_stage_rr<real, TW>(A, chain, it, r0 - 1, HB + 2, RR, SS);
       __syncthreads();
       for (int col = col0; col < g.nx; col += MB_W * BAND_BT) {
         if (col != col0) load_x(col, xr);
@@ -206,7 +207,7 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
 #pragma unroll
             for (int q = 0; q < MB_W; ++q) xv.a[q] = real(0);
           }
-          stp<real, MB_W>(SOL + a * pitch + BAND_PAD + col, mband_sol(RR, SS, pitch, a + 1, col, xv, A.tv_gamma));
+          stp<real, MB_W>(SOL + a * pitch + BAND_PAD + col, mband_sol<real, MB_W>(RR, SS, pitch, a + 1, col, xv, A.tv_gamma));
         }
       }
       __syncthreads();
@@ -263,7 +264,7 @@ __device__ __forceinline__ void mb_st4(real* p, const Pack<real, 4>& v, int n, b
 }
 
 // ---------------------------------------------------------------- phase U
-template <typename real>
+template <typename real, int TW>
 __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long long n, real* smem) {
   constexpr int RB = MB_RB, HB = MB_HB;
   const Geom<real>& g = A.g;
@@ -287,7 +288,7 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
     const int kf = A.st[chain].kf;
     for (int r0 = i0; r0 < i0 + RB && r0 < g.ny; r0 += HB) {
       if (r0 != i0) __syncthreads();
-      mband_stage_rr(A, chain, kf, r0 - 1, HB + 1, RR, SS);
+      mband_stage_rr<real, TW>(A, chain, kf, r0 - 1, HB + 1, RR, SS);
       __syncthreads();
       // each thread: 4 consecutive pixels of one row (one Philox block of normals), moved as one 16/32-byte access
       // per array when the rows allow it; all loads of the quad are issued before its arithmetic
@@ -336,7 +337,7 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
   }
 }
 
-template <typename real, int NT, int GW>
+template <typename real, int NT, int GW, int TW>
 __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid_constant__ MyulaArgs<real> A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
@@ -359,12 +360,12 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid
       if (*(volatile int*)A.n_active == 0) break;
       grid.sync();   // everyone has read n_active before it is reset
       if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-      mband_tv_sweep<real>(A, sched, it, smem, red);
+      mband_tv_sweep<real, TW>(A, sched, it, smem, red);
       grid.sync();
       phase_tv_scalar(A, it);
       grid.sync();
     }
-    mband_update<real>(A, sched, n, smem);
+    mband_update<real, TW>(A, sched, n, smem);
     grid.sync();
   }
 }

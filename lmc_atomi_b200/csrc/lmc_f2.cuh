@@ -99,6 +99,7 @@ template <typename real> struct Lanes {
   __device__ __forceinline__ static mask gt(real a, real b) { return a > b; }
   __device__ __forceinline__ static mask lt(real a, real b) { return a < b; }
   __device__ __forceinline__ static mask not_(mask m) { return !m; }
+  __device__ __forceinline__ static bool any(mask m) { return m; }
   __device__ __forceinline__ static real select(mask m, real a, real b) { return m ? a : b; }
   __device__ __forceinline__ static void count_add(count& n, mask m) { n += m ? 1u : 0u; }
   __device__ __forceinline__ static void dbl_add(dbl& a, real b) { a += (double)b; }
@@ -123,6 +124,7 @@ template <> struct Lanes<f2> {
   __device__ __forceinline__ static mask gt(f2 a, f2 b) { return b2{a.x > b.x, a.y > b.y}; }
   __device__ __forceinline__ static mask lt(f2 a, f2 b) { return b2{a.x < b.x, a.y < b.y}; }
   __device__ __forceinline__ static mask not_(mask m) { return b2{!m.x, !m.y}; }
+  __device__ __forceinline__ static bool any(mask m) { return m.x || m.y; }
   __device__ __forceinline__ static f2 select(mask m, f2 a, f2 b) { return f2(m.x ? a.x : b.x, m.y ? a.y : b.y); }
   __device__ __forceinline__ static void count_add(count& n, mask m) { n.x += m.x ? 1u : 0u; n.y += m.y ? 1u : 0u; }
   __device__ __forceinline__ static void dbl_add(dbl& a, f2 b) { a.x += (double)b.x; a.y += (double)b.y; }

@@ -22,6 +22,14 @@ namespace {
 constexpr int NMAX = LMC_MAX_COMP;
 constexpr int BLOCK = 256;
 
+// build-time experiment switches (defaults = the shipped configuration; see profiles/r02g_mix_variants.txt)
+#ifndef LMC_MIX_NOSHIFT
+#define LMC_MIX_NOSHIFT 0
+#endif
+#ifndef LMC_MIX_MINBLOCKS
+#define LMC_MIX_MINBLOCKS 1
+#endif
+
 template <typename real>
 struct MixP {
   int n, t;
@@ -128,6 +136,7 @@ __device__ __forceinline__ void eval_gauss(const MixP<real>& P, real t0, real t1
 template <typename real, int NC, bool HESS>
 __device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real t1, Eval<real>& e) {
   using M = Math<real>;
+  using L = Lanes<real>;
   const int n = NC > 0 ? NC : P.n;
   real a[NMAX], r0[NMAX], r1[NMAX];
   real amax = real(-1e30);
@@ -140,37 +149,56 @@ __device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real 
       real s1n = M::abs(d0 - r0[i]) + M::abs(d1 - r1[i]);
       real rr = M::fma(r0[i], r0[i], r1[i] * r1[i]);
       a[i] = M::fma(rr, P.c2, M::fma(s1n, P.c1[i], P.lc[i]));   // log2(omega_i pdf_lamda,i)
-      amax = M::max(amax, a[i]);
+      if (!LMC_MIX_NOSHIFT || M::is_double) amax = M::max(amax, a[i]);
     }
   }
-  real S = 0, gp0 = 0, gp1 = 0, hp00 = 0, hp01 = 0, hp11 = 0;
+  real S, gp0, gp1, hp00 = real(0), hp01 = real(0), hp11 = real(0);
   const real l1 = M::abs(t0) + M::abs(t1);
+  auto sums = [&](real shift) {
+    S = real(0); gp0 = real(0); gp1 = real(0);
 #pragma unroll
-  for (int i = 0; i < NMAX; ++i) {
-    if (i < n) {
-      real w = M::exp2(a[i] - amax);
-      S += w;
-      gp0 = M::fma(w, r0[i], gp0);
-      gp1 = M::fma(w, r1[i], gp1);
-      if (HESS) {
-        // lmc_laplace.py:80-82 (sic): weight (alpha/2)^2 exp(-alpha ||theta||_1), no mu,
-        // unsmoothed exponent; matrix (-I + g g^T) with g = r / lamda.
-        real v0 = r0[i] * P.inv_lamda, v1 = r1[i] * P.inv_lamda;
-        real wq = M::exp2(M::fma(l1, P.c1[i], P.lc[i]) - amax);
-        hp00 = M::fma(wq, M::fma(v0, v0, real(-1)), hp00);
-        hp01 = M::fma(wq, v0 * v1, hp01);
-        hp11 = M::fma(wq, M::fma(v1, v1, real(-1)), hp11);
+    for (int i = 0; i < NMAX; ++i) {
+      if (i < n) {
+        real w = M::exp2(a[i] - shift);
+        S += w;
+        gp0 = M::fma(w, r0[i], gp0);
+        gp1 = M::fma(w, r1[i], gp1);
+        if (HESS) {
+          // lmc_laplace.py:80-82 (sic): weight (alpha/2)^2 exp(-alpha ||theta||_1), no mu,
+          // unsmoothed exponent; matrix (-I + g g^T) with g = r / lamda.
+          real v0 = r0[i] * P.inv_lamda, v1 = r1[i] * P.inv_lamda;
+          real wq = M::exp2(M::fma(l1, P.c1[i], P.lc[i]) - shift);
+          hp00 = M::fma(wq, M::fma(v0, v0, real(-1)), hp00);
+          hp01 = M::fma(wq, v0 * v1, hp01);
+          hp11 = M::fma(wq, M::fma(v1, v1, real(-1)), hp11);
+        }
       }
     }
+  };
+  if (LMC_MIX_NOSHIFT && !M::is_double && !HESS) {
+    // fp32 production: the exponents a_i are <= lc_i <= 0, so 2^a_i cannot overflow; the log-sum-exp shift is only
+    // needed when EVERY component underflows (a chain > 170 / alpha away from all modes), handled by the rare
+    // second evaluation below.  Saves the running max and the five subtractions of every evaluation.
+    amax = real(0);
+    sums(real(0));
+    if (L::any(L::lt(S, real(1e-30)))) {
+      amax = real(-1e30);
+#pragma unroll
+      for (int i = 0; i < NMAX; ++i)
+        if (i < n) amax = M::max(amax, a[i]);
+      sums(amax);
+    }
+  } else {
+    sums(amax);
   }
   const real rS = M::rcp(S), gS = rS * P.inv_lamda;
   e.g0 = gp0 * gS;
   e.g1 = gp1 * gS;
   e.logp2 = amax + M::log2(S);
   if (HESS) {
-    e.h00 = M::fma(e.g0, e.g0, -hp00 * rS);
-    e.h01 = M::fma(e.g0, e.g1, -hp01 * rS);
-    e.h11 = M::fma(e.g1, e.g1, -hp11 * rS);
+    e.h00 = M::fma(e.g0, e.g0, -(hp00 * rS));
+    e.h01 = M::fma(e.g0, e.g1, -(hp01 * rS));
+    e.h11 = M::fma(e.g1, e.g1, -(hp11 * rS));
   }
 }
 
@@ -514,7 +542,7 @@ template <> struct ScalarOf<f2> { using type = float; };
 // real = f2 (production fp32): every thread advances TWO chains, lanes x / y of the packed type, chains
 // item*64 + lane and item*64 + 32 + lane (both halves of a warp's loads and stores stay coalesced).
 template <typename real, int TARGET, int ALG, int NC, bool PROD>
-__global__ void __launch_bounds__(BLOCK) mix_chain_kernel(const __grid_constant__ MixP<real> P,
+__global__ void __launch_bounds__(BLOCK, (Lanes<real>::N == 2 ? LMC_MIX_MINBLOCKS : 1)) mix_chain_kernel(const __grid_constant__ MixP<real> P,
                                                           const __grid_constant__ MixIo io) {
   using M = Math<real>;
   using L = Lanes<real>;
@@ -790,6 +818,12 @@ template <typename real>
 int dispatch(const lmc_mix_target& T, const lmc_mix_step& S, const MixIo& io, cudaStream_t st) {
 #define LMC_CASE(TG, AL) \
   if (T.kind == TG && S.alg == AL) return launch_nc<real, TG, AL>(T, S, io, st);
+#ifdef LMC_MIX_BENCH_ONLY   // experiment builds: only the samplers bench.py times (fast to compile)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_ULA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_MALA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_PULA)
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_MLA)
+#else
   LMC_CASE(LMC_TARGET_GAUSS, LMC_ULA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_MALA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_PULA)
@@ -806,6 +840,7 @@ int dispatch(const lmc_mix_target& T, const lmc_mix_step& S, const MixIo& io, cu
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_PPULA)
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_FBULA)
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_LBMUMLA)
+#endif
 #undef LMC_CASE
   lmc_set_error("lmc_mix_run: sampler %d is not defined for target kind %d", S.alg, T.kind);
   return -1;

@@ -31,7 +31,7 @@ __all__ = ["AdaptivePrimalDual"]
 
 
 def AdaptivePrimalDual(proxf, proxg, A, x0, tau, mu, alpha=0.5, eta=0.95, s=1., delta=1.5, z=None, niter=10,
-                       tol=1e-10, callback=None, show=False, dtype="float64", device_metrics=None):
+                       tol=1e-10, callback=None, show=False, dtype="float64", device_metrics=None, trace=None):
     """Returns ``(x, steps)`` like pyproximal: the final iterate (P,) float64 and the (niter, 3) array of
     (tau, mu, alpha) after each iteration.  ``device_metrics``: an ``algs.DeviceMetrics`` collecting the driver's
     callback quantities on the GPU instead of a per-iteration host ``callback``."""
@@ -90,6 +90,8 @@ def AdaptivePrimalDual(proxf, proxg, A, x0, tau, mu, alpha=0.5, eta=0.95, s=1., 
         elif p < s * d / delta:
             tau, mu, alpha = tau * (1 - alpha), mu / (1 - alpha), alpha * eta
         steps[iiter] = (tau, mu, alpha)
+        if trace is not None:       # debugging aid: residuals and the LSQR work of every iteration
+            trace.append({"p": p, "d": d, "tau": tau, "mu": mu, **eng.read_counters()})
         if device_metrics is not None:
             device_metrics._extend(eng.sample_metrics(x, device_metrics.xtrue, g_sigma, iso))
         if callback is not None or (show and algs._show_line(iiter, niter)):

@@ -332,6 +332,7 @@ def test_ulpda_band_work_queue_many_chains(torch, dims, Cn, dtype, tol):
 
 
 @pytest.mark.parametrize("dims,kernel", [((64, 64), 5), ((40, 52), 5), ((23, 30), 5), ((70, 96), 5), ((9, 4), 5),
+                                         ((33, 95), 5), ((41, 77), 6), ((20, 301), 7),
                                          ((40, 52), 6), ((33, 96), 7), ((64, 64), 7)])
 def test_myula_band_trajectory_fp64(torch, dims, kernel):
     """Row-band MYULA kernel (img_myula_band.inl) against the oracle: ragged last band / sub-band, narrow images,

@@ -46,12 +46,14 @@ def noise(torch, einstein):
     return z
 
 
-def residuals(curves, fig, res):
+def residuals(curves, fig, res, max_idx=None):
     out = {}
     for (term, k), m in MODEL_OF.items():
         r = res["models"][f"{term}_{k}"]
         for name in ("snr", "psnr", "mse"):
             idx, val = curves[f"{fig}_{name}_M{m}_idx"], curves[f"{fig}_{name}_M{m}_val"]
+            if max_idx is not None:
+                idx, val = idx[idx <= max_idx], val[idx <= max_idx]
             got = np.asarray(r[name])[idx]
             d = np.abs(got - val)
             if name == "mse":      # to dB, so one tolerance serves (the MSE axis resolves 1.1e-4 absolute)
@@ -82,10 +84,25 @@ def test_einstein_map_matches_reference_figure(torch, einstein):
     curves = np.load(os.path.join(GOLDEN, "deconv_curves.npz"))
     res = prox_lmc_deconv(gamma_mc=15., gamma_me=15., sigma=0.75, tau=0.3, niter_MAP=N, image=einstein,
                           compute_MAP=True, seed=0, dtype="float64")
+    # The driver's step sizes violate the PDHG condition tau mu ||G||^2 < 1 (0.534 x 1 x 8 = 4.3): the
+    # iteration settles on a bounded oscillation (residuals p, d ~ 40, never 0) that amplifies rounding differences
+    # about 10x per 25 iterations (measured GPU vs CPU oracle, scripts/debug_map.py: 1e-16 -> 1e-9 by iteration 190,
+    # identical LSQR iteration counts throughout).  Beyond ~150 iterations no two floating-point implementations
+    # (including the reference's own FFT blur) agree to the plot's resolution, so the gate is tight on the early
+    # iterates (which pin every rule of the iteration, the step-size adaptations included) and loose on the tail.
+    # Measured (profiles/r02f_pinned_MAP.json): first 120 iterations within 1.1e-7 dB for the L2 / ME-TV models and
+    # 6e-6 dB for the MC-TV models (anisotropic prior, faster amplification); whole run within 3e-3 dB.
+    first50 = residuals(curves, "einstein_MAP", res, max_idx=50)
+    first120 = residuals(curves, "einstein_MAP", res, max_idx=120)
     worst = residuals(curves, "einstein_MAP", res)
     os.makedirs("gpurun_out", exist_ok=True)
     with open("gpurun_out/pinned_MAP.json", "w") as f:
-        json.dump({"worst_abs_diff_db": worst,
+        json.dump({"worst_abs_diff_db_first_50": first50, "worst_abs_diff_db_first_120": first120,
+                   "worst_abs_diff_db": worst,
                    "map_psnr": {k: v["map_psnr"] for k, v in res["models"].items()}}, f, indent=1)
-    bad = {k: v for k, v in worst.items() if not v < DB_TOL}
+    bad = {k: v for k, v in first50.items() if not v < DB_TOL}
+    assert not bad, bad
+    bad = {k: v for k, v in first120.items() if not v < 2e-5}
+    assert not bad, bad
+    bad = {k: v for k, v in worst.items() if not v < 0.02}
     assert not bad, bad

@@ -103,3 +103,25 @@ def test_headless_main_returns_the_wasserstein_curves():
     assert set(w) == {"ula", "mala", "pula", "mla"} and len(w["pula"]) == 3
     want = W.wasserstein2_curve(out["true_samples"], out["pula"], interval=100)
     assert np.abs(np.array(w["pula"]) - np.array(want)).max() < TOL
+
+
+def test_sinkhorn_w2_at_driver_scale_matches_exact_assignment():
+    """K = 5000, the drivers' default number of true samples (lmc.py:194-196), where the transport LP is out of the
+    oracle's reach: for two uniformly weighted sets of EQUAL size the optimal plan is a permutation (Birkhoff), so
+    scipy's linear_sum_assignment gives the exact EMD that POT's network simplex returns.  Reference-shaped sets:
+    true samples of the 5-component Gaussian mixture vs a CUDA ULA chain of the same length."""
+    from scipy.optimize import linear_sum_assignment
+    from lmc_atomi_b200 import w2
+    K = 5000
+    z, s, _ = make_samplers(K=K)["gauss"]
+    chain = s.ula(float(z["gamma"]))
+    true = s.true_samples()
+    assert true.shape == chain.shape == (K, 2)
+    C = ((true[:, None, :] - chain[None, :, :]) ** 2).sum(-1)
+    r, c = linear_sum_assignment(C)
+    exact = float(np.sqrt(C[r, c].mean()))
+    ev = w2.SinkhornW2(true)
+    got = ev.distance(chain)
+    print(f"W2 at K={K}: sinkhorn {got:.6f} exact {exact:.6f} diff {got - exact:+.2e} iters {ev.last['iters']}")
+    assert ev.last["converged"]
+    assert abs(got - exact) < TOL
