@@ -23,11 +23,14 @@ constexpr int NMAX = LMC_MAX_COMP;
 constexpr int BLOCK = 256;
 
 // build-time experiment switches (defaults = the shipped configuration; see profiles/r02g_mix_variants.txt)
+// A/B on B200 at the benchmark shape (profiles/r02h_mix_variants.txt, G chain-steps/s, reproducible to 0.5 %):
+//   shift + no hint 173.7 | shift + 3 CTAs/SM 176.7 | no-shift + no hint 176.9 | no-shift + 2 CTAs/SM 188.3 (shipped)
+//   | no-shift + 3 CTAs/SM 186.5 | no-shift + 4 CTAs/SM 183.8        (scalar one-chain-per-thread kernels: 169.4)
 #ifndef LMC_MIX_NOSHIFT
-#define LMC_MIX_NOSHIFT 0
+#define LMC_MIX_NOSHIFT 1
 #endif
 #ifndef LMC_MIX_MINBLOCKS
-#define LMC_MIX_MINBLOCKS 1
+#define LMC_MIX_MINBLOCKS 2
 #endif
 
 template <typename real>
@@ -90,7 +93,9 @@ constexpr float LOG2E_F = 1.4426950408889634f;
 template <typename real, int NC, bool HESS>
 __device__ __forceinline__ void eval_gauss(const MixP<real>& P, real t0, real t1, Eval<real>& e) {
   using M = Math<real>;
+  using L = Lanes<real>;
   const int n = NC > 0 ? NC : P.n;
+  constexpr bool NOSHIFT = LMC_MIX_NOSHIFT && !M::is_double && !HESS;   // see eval_laplace
   real a[NMAX], v0[NMAX], v1[NMAX];
   real amax = real(-1e30);
 #pragma unroll
@@ -101,32 +106,48 @@ __device__ __forceinline__ void eval_gauss(const MixP<real>& P, real t0, real t1
       v1[i] = M::fma(P.p10[i], d0, P.p11[i] * d1);
       real fac = M::fma(d0, v0[i], d1 * v1[i]);
       a[i] = M::fma(fac, real(-0.5 * 1.4426950408889634), P.lc[i]);
-      amax = M::max(amax, a[i]);
+      if (!NOSHIFT) amax = M::max(amax, a[i]);
     }
   }
-  real S = 0, gp0 = 0, gp1 = 0, hp00 = 0, hp01 = 0, hp11 = 0;
+  real S, gp0, gp1, hp00 = real(0), hp01 = real(0), hp11 = real(0);
+  auto sums = [&](real shift) {
+    S = real(0); gp0 = real(0); gp1 = real(0);
 #pragma unroll
-  for (int i = 0; i < NMAX; ++i) {
-    if (i < n) {
-      real w = M::exp2(a[i] - amax);
-      S += w;
-      gp0 = M::fma(w, v0[i], gp0);  // note: this is -grad p (sign folded)
-      gp1 = M::fma(w, v1[i], gp1);
-      if (HESS) {  // lmc.py:63-65: N_i (P d d^T P - P)
-        hp00 = M::fma(w, M::fma(v0[i], v0[i], -P.p00[i]), hp00);
-        hp01 = M::fma(w, M::fma(v0[i], v1[i], -real(0.5) * (P.p01[i] + P.p10[i])), hp01);
-        hp11 = M::fma(w, M::fma(v1[i], v1[i], -P.p11[i]), hp11);
+    for (int i = 0; i < NMAX; ++i) {
+      if (i < n) {
+        real w = M::exp2(a[i] - shift);
+        S += w;
+        gp0 = M::fma(w, v0[i], gp0);  // note: this is -grad p (sign folded)
+        gp1 = M::fma(w, v1[i], gp1);
+        if (HESS) {  // lmc.py:63-65: N_i (P d d^T P - P)
+          hp00 = M::fma(w, M::fma(v0[i], v0[i], -P.p00[i]), hp00);
+          hp01 = M::fma(w, M::fma(v0[i], v1[i], -(real(0.5) * (P.p01[i] + P.p10[i]))), hp01);
+          hp11 = M::fma(w, M::fma(v1[i], v1[i], -P.p11[i]), hp11);
+        }
       }
     }
+  };
+  if (NOSHIFT) {
+    amax = real(0);
+    sums(real(0));
+    if (L::any(L::lt(S, real(1e-30)))) {   // every component underflowed: redo with the max shift
+      amax = real(-1e30);
+#pragma unroll
+      for (int i = 0; i < NMAX; ++i)
+        if (i < n) amax = M::max(amax, a[i]);
+      sums(amax);
+    }
+  } else {
+    sums(amax);
   }
   real rS = M::rcp(S);
   e.g0 = gp0 * rS;
   e.g1 = gp1 * rS;
   e.logp2 = amax + M::log2(S);
   if (HESS) {  // lmc.py:71-75: grad p grad p^T / p^2 - hess p / p
-    e.h00 = M::fma(e.g0, e.g0, -hp00 * rS);
-    e.h01 = M::fma(e.g0, e.g1, -hp01 * rS);
-    e.h11 = M::fma(e.g1, e.g1, -hp11 * rS);
+    e.h00 = M::fma(e.g0, e.g0, -(hp00 * rS));
+    e.h01 = M::fma(e.g0, e.g1, -(hp01 * rS));
+    e.h11 = M::fma(e.g1, e.g1, -(hp11 * rS));
   }
 }
 
@@ -138,6 +159,7 @@ __device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real 
   using M = Math<real>;
   using L = Lanes<real>;
   const int n = NC > 0 ? NC : P.n;
+  constexpr bool NOSHIFT = LMC_MIX_NOSHIFT && !M::is_double && !HESS;
   real a[NMAX], r0[NMAX], r1[NMAX];
   real amax = real(-1e30);
 #pragma unroll
@@ -149,7 +171,7 @@ __device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real 
       real s1n = M::abs(d0 - r0[i]) + M::abs(d1 - r1[i]);
       real rr = M::fma(r0[i], r0[i], r1[i] * r1[i]);
       a[i] = M::fma(rr, P.c2, M::fma(s1n, P.c1[i], P.lc[i]));   // log2(omega_i pdf_lamda,i)
-      if (!LMC_MIX_NOSHIFT || M::is_double) amax = M::max(amax, a[i]);
+      if (!NOSHIFT) amax = M::max(amax, a[i]);
     }
   }
   real S, gp0, gp1, hp00 = real(0), hp01 = real(0), hp11 = real(0);
@@ -175,10 +197,11 @@ __device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real 
       }
     }
   };
-  if (LMC_MIX_NOSHIFT && !M::is_double && !HESS) {
-    // fp32 production: the exponents a_i are <= lc_i <= 0, so 2^a_i cannot overflow; the log-sum-exp shift is only
-    // needed when EVERY component underflows (a chain > 170 / alpha away from all modes), handled by the rare
-    // second evaluation below.  Saves the running max and the five subtractions of every evaluation.
+  if (NOSHIFT) {
+    // fp32: every exponent a_i is <= lc_i = log2(omega_i x normalising constant), a finite per-component constant,
+    // so 2^a_i cannot overflow unless the constant itself does; the log-sum-exp shift is only needed when EVERY
+    // component underflows (a chain ~170 / alpha away from all modes), handled by the rare second evaluation below.
+    // Saves the running max and the n subtractions of every evaluation (profiles/r02h_mix_variants.txt).
     amax = real(0);
     sums(real(0));
     if (L::any(L::lt(S, real(1e-30)))) {
@@ -814,26 +837,49 @@ int launch_nc(const lmc_mix_target& T, const lmc_mix_step& S, MixIo io, cudaStre
   return prod ? launch_one<real, TARGET, ALG, 0, true>(P, io, st) : launch_one<real, TARGET, ALG, 0, false>(P, io, st);
 }
 
-template <typename real>
-int dispatch(const lmc_mix_target& T, const lmc_mix_step& S, const MixIo& io, cudaStream_t st) {
+// The 16 sampler x target instantiations (x {f2, float, double} x {production, validation}) are compiled in three
+// translation units, one per target kind (mix_gauss.cu, mix_laplace.cu, mix_prox.cu define LMC_MIX_TU and include
+// this file), so that nvcc builds them in parallel; this file alone (LMC_MIX_TU 0) is the API + dispatch.
+#ifndef LMC_MIX_TU
+#define LMC_MIX_TU 0
+#endif
+}  // namespace
+int lmc_mix_dispatch_gauss(const lmc_mix_target* T, const lmc_mix_step* S, int dtype, const void* io, cudaStream_t st);
+int lmc_mix_dispatch_laplace(const lmc_mix_target* T, const lmc_mix_step* S, int dtype, const void* io, cudaStream_t st);
+int lmc_mix_dispatch_prox(const lmc_mix_target* T, const lmc_mix_step* S, int dtype, const void* io, cudaStream_t st);
+namespace {
+
 #define LMC_CASE(TG, AL) \
-  if (T.kind == TG && S.alg == AL) return launch_nc<real, TG, AL>(T, S, io, st);
-#ifdef LMC_MIX_BENCH_ONLY   // experiment builds: only the samplers bench.py times (fast to compile)
-  LMC_CASE(LMC_TARGET_LAPLACE, LMC_ULA)
-  LMC_CASE(LMC_TARGET_LAPLACE, LMC_MALA)
-  LMC_CASE(LMC_TARGET_LAPLACE, LMC_PULA)
-  LMC_CASE(LMC_TARGET_LAPLACE, LMC_MLA)
-#else
+  if (S.alg == AL) return dtype == LMC_F64 ? launch_nc<double, TG, AL>(T, S, io, st) : launch_nc<float, TG, AL>(T, S, io, st);
+#if LMC_MIX_TU == 1 || defined(LMC_MIX_BENCH_ONLY)
+int dispatch_gauss(const lmc_mix_target& T, const lmc_mix_step& S, int dtype, const MixIo& io, cudaStream_t st) {
+#ifndef LMC_MIX_BENCH_ONLY
   LMC_CASE(LMC_TARGET_GAUSS, LMC_ULA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_MALA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_PULA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_IHPULA)
   LMC_CASE(LMC_TARGET_GAUSS, LMC_MLA)
+#endif
+  lmc_set_error("lmc_mix_run: sampler %d is not defined for the Gaussian mixture", S.alg);
+  return -1;
+}
+#endif
+#if LMC_MIX_TU == 2 || defined(LMC_MIX_BENCH_ONLY)
+int dispatch_laplace(const lmc_mix_target& T, const lmc_mix_step& S, int dtype, const MixIo& io, cudaStream_t st) {
   LMC_CASE(LMC_TARGET_LAPLACE, LMC_ULA)
   LMC_CASE(LMC_TARGET_LAPLACE, LMC_MALA)
   LMC_CASE(LMC_TARGET_LAPLACE, LMC_PULA)
-  LMC_CASE(LMC_TARGET_LAPLACE, LMC_IHPULA)
   LMC_CASE(LMC_TARGET_LAPLACE, LMC_MLA)
+#ifndef LMC_MIX_BENCH_ONLY
+  LMC_CASE(LMC_TARGET_LAPLACE, LMC_IHPULA)
+#endif
+  lmc_set_error("lmc_mix_run: sampler %d is not defined for the Laplacian mixture", S.alg);
+  return -1;
+}
+#endif
+#if LMC_MIX_TU == 3 || defined(LMC_MIX_BENCH_ONLY)
+int dispatch_prox(const lmc_mix_target& T, const lmc_mix_step& S, int dtype, const MixIo& io, cudaStream_t st) {
+#ifndef LMC_MIX_BENCH_ONLY
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_PGLD)
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_MYULA)
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_MYMALA)
@@ -841,11 +887,32 @@ int dispatch(const lmc_mix_target& T, const lmc_mix_step& S, const MixIo& io, cu
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_FBULA)
   LMC_CASE(LMC_TARGET_GAUSS_L1, LMC_LBMUMLA)
 #endif
-#undef LMC_CASE
-  lmc_set_error("lmc_mix_run: sampler %d is not defined for target kind %d", S.alg, T.kind);
+  lmc_set_error("lmc_mix_run: sampler %d is not defined for the Gaussian mixture x Laplacian prior", S.alg);
   return -1;
 }
+#endif
+#undef LMC_CASE
 
+}  // namespace
+
+#if LMC_MIX_TU == 1 || defined(LMC_MIX_BENCH_ONLY)
+int lmc_mix_dispatch_gauss(const lmc_mix_target* T, const lmc_mix_step* S, int dtype, const void* io, cudaStream_t st) {
+  return dispatch_gauss(*T, *S, dtype, *static_cast<const MixIo*>(io), st);
+}
+#endif
+#if LMC_MIX_TU == 2 || defined(LMC_MIX_BENCH_ONLY)
+int lmc_mix_dispatch_laplace(const lmc_mix_target* T, const lmc_mix_step* S, int dtype, const void* io, cudaStream_t st) {
+  return dispatch_laplace(*T, *S, dtype, *static_cast<const MixIo*>(io), st);
+}
+#endif
+#if LMC_MIX_TU == 3 || defined(LMC_MIX_BENCH_ONLY)
+int lmc_mix_dispatch_prox(const lmc_mix_target* T, const lmc_mix_step* S, int dtype, const void* io, cudaStream_t st) {
+  return dispatch_prox(*T, *S, dtype, *static_cast<const MixIo*>(io), st);
+}
+#endif
+
+#if LMC_MIX_TU == 0
+namespace {
 inline uint2 make_key(uint64_t seed) { return make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)); }
 
 }  // namespace
@@ -906,7 +973,13 @@ extern "C" int lmc_mix_run(const lmc_mix_target* target, const lmc_mix_step* ste
   io.n_items = (int)items_for(dtype, io, C);
 
   LMC_CUDA_OK(cudaMemsetAsync(io.queue, 0, 256, st));
-  int rc = dtype == LMC_F64 ? dispatch<double>(*target, *step, io, st) : dispatch<float>(*target, *step, io, st);
+  int rc = -1;
+  switch (target->kind) {
+    case LMC_TARGET_GAUSS: rc = lmc_mix_dispatch_gauss(target, step, dtype, &io, st); break;
+    case LMC_TARGET_LAPLACE: rc = lmc_mix_dispatch_laplace(target, step, dtype, &io, st); break;
+    case LMC_TARGET_GAUSS_L1: rc = lmc_mix_dispatch_prox(target, step, dtype, &io, st); break;
+    default: lmc_set_error("lmc_mix_run: unknown target kind %d", target->kind);
+  }
   if (rc != 0) return rc;
   if (uio->d_moments != nullptr) {
     mix_reduce_moments<<<1, 256, 0, st>>>(io.partial, io.n_items, uio->d_moments);
@@ -931,3 +1004,4 @@ extern "C" int lmc_mix_philox_draws(int dtype, int adjusted, int64_t C, int64_t 
   LMC_CUDA_OK(cudaGetLastError());
   return 0;
 }
+#endif  // LMC_MIX_TU == 0

@@ -1,0 +1,3 @@
+// Translation unit 2 of the mixture-chain kernels: the instantiations of one target kind (see mix_kernels.cu).
+#define LMC_MIX_TU 2
+#include "mix_kernels.cu"

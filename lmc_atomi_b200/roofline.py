@@ -3,12 +3,13 @@
 Two kinds of bound appear on this path:
 
 * ISSUE (mixture chains, on-chip MYULA): the state lives in registers / shared memory, HBM traffic is ~0, so the
-  binding resource is the instruction issue rate: 148 SMs x 4 sub-partitions x 1 warp-instruction per clock
-  = 148 x 128 thread-instructions per clock.  `frac` = EXECUTED thread-instructions per unit (SASS count from the
-  committed ncu capture: smsp__inst_executed x 32 / units) x units/s / peak.  This equals ncu's
-  smsp__issue_active and can never exceed 1.  The survey's ALGORITHMIC lane-op count (one op per + - x / max abs
-  compare, FMA = 2) is reported beside it as `algorithmic_frac`; it can exceed the executed figure because an FMA
-  retires two algorithmic ops in one instruction.
+  binding resource is instruction dispatch: 148 SMs x 4 sub-partitions x 1 warp-instruction per clock
+  = 148 x 128 thread-instructions per clock.  `frac` = dispatch slots per unit x units/s / peak, where the slots are
+  the EXECUTED thread-instructions (ncu: smsp__inst_executed x 32 / units) with packed FP32 instructions counted
+  twice (they occupy the dispatch port for two cycles on B200); `frac_issue_only` (= ncu smsp__issue_active) counts
+  them once.  Neither can exceed 1.  The survey's ALGORITHMIC lane-op count (one op per + - x / max abs compare,
+  FMA = 2) is reported beside them as `algorithmic_frac`; it can exceed the executed figure because an FMA retires
+  two algorithmic ops in one instruction.
 * HBM (band / tile image kernels): `frac` = algorithmic bytes per unit ((12+9j) / (24+16k) array-element
   transfers per pixel-iteration) x units/s / measured copy bandwidth; `frac_measured_dram` = DRAM bytes ncu measured
   per unit x units/s / the same peak (lower than `frac` when re-reads hit the 126 MB L2); `frac_min_traffic` = the
@@ -65,25 +66,36 @@ def mix_laneops_per_step(target: str, alg: str, t: int = 100) -> float:
 
 
 # ---- mixture chains: EXECUTED thread-instructions per chain-step of the production kernels on the Laplacian
-# mixture (n = 5), from the `ncu --set full` capture named in MIX_PROFILE: smsp__inst_executed.sum x 32 / (C x K).
-# Keyed by dtype; refreshed whenever mix_kernels.cu changes (the capture is re-taken by scripts/gpu_profile_mix.sh).
-MIX_PROFILE = "profiles/r01e_mix_ncu_full_summary.csv"
-MIX_SASS_INSTR_PER_STEP = {"float32": {"ula": 150.4, "mala": 204.1, "pula": 157.0, "mla": 182.5}}
-MIX_ISSUE_ACTIVE_PCT = {"ula": 83.0, "mala": 78.3, "pula": 84.4, "mla": 78.3}       # smsp__issue_active, same capture
-MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 125.2e3, "mala": 104.7e3, "pula": 126.5e3, "mla": 131.6e3}   # state is in registers
+# mixture (n = 5), from the `ncu --set full` capture named in MIX_PROFILE: smsp__inst_executed.sum x 32 / (C x K), and
+# the share of them that are packed FP32 instructions (FADD2 / FMUL2 / FFMA2) from the SASS census of the steady-state
+# loop (scripts/sass_loop_census.py -> MIX_CENSUS).  A packed instruction holds the dispatch port for two cycles on
+# B200 (profiles/r02c_ubench_issue.txt: FFMA2 0.5 vs FFMA 1.0 warp-instructions / clock / sub-partition), so the
+# dispatch slots a step needs are instr x (1 + packed share).  Refreshed whenever mix_kernels.cu changes.
+MIX_PROFILE = "profiles/r02i_mix_ncu_full_summary.csv"
+MIX_CENSUS = "profiles/r02i_mix_sass_census.txt"
+MIX_SASS_INSTR_PER_STEP = {"float32": {"ula": 106.4, "mala": 155.3, "pula": 112.6, "mla": 132.4}}
+MIX_PACKED_SHARE = {"float32": {"ula": 0.368, "mala": 0.303, "pula": 0.383, "mla": 0.333}}
+MIX_ISSUE_ACTIVE_PCT = {"ula": 67.2, "mala": 65.4, "pula": 67.9, "mla": 61.6}       # smsp__issue_active, same capture
+MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 150.0e3, "mala": 116.7e3, "pula": 150.0e3, "mla": 153.3e3}   # state is in registers
 
 
 def mix_roofline(alg: str, chain_steps_per_sec: float, sm_mhz: float, dtype: str = "float32"):
-    """Roofline object of one production mixture kernel at the measured rate (per GPU)."""
+    """Roofline object of one production mixture kernel at the measured rate (per GPU): `frac` = dispatch-slot
+    fraction = executed thread-instructions x (1 + packed share) x rate / (148 x 128 x f)."""
     peak = issue_peak_laneops(sm_mhz)
     sass = MIX_SASS_INSTR_PER_STEP.get(dtype, {}).get(alg)
+    packed = MIX_PACKED_SHARE.get(dtype, {}).get(alg)
     algo = mix_laneops_per_step("laplace", alg)
     out = {"bound": "issue", "unit": "Tthread-inst/s", "peak": peak / 1e12,
            "algorithmic_laneops_per_step": algo, "algorithmic_frac": algo * chain_steps_per_sec / peak,
-           "sass_thread_instr_per_step": sass, "profile": MIX_PROFILE}
-    if sass is not None:
-        out["achieved"] = sass * chain_steps_per_sec / 1e12
-        out["frac"] = sass * chain_steps_per_sec / peak
+           "sass_thread_instr_per_step": sass, "packed_fp32_share": packed, "profile": MIX_PROFILE,
+           "census": MIX_CENSUS}
+    if sass is not None and packed is not None:
+        slots = sass * (1.0 + packed)
+        out["dispatch_slots_per_step"] = slots
+        out["achieved"] = slots * chain_steps_per_sec / 1e12
+        out["frac"] = slots * chain_steps_per_sec / peak
+        out["frac_issue_only"] = sass * chain_steps_per_sec / peak       # = ncu smsp__issue_active
     else:        # no capture of this instantiation: only the algorithmic figure is known
         out["achieved"] = None
         out["frac"] = None

@@ -1,23 +1,24 @@
-"""TEST INFRASTRUCTURE ONLY -- CPU oracle for the image (deconvolution) samplers.
+"""TEST INFRASTRUCTURE ONLY -- CPU oracle for the image (deconvolution) samplers and the MAP branch.
 
-PARITY UNPINNED against the third-party libraries: the per-iteration arithmetic of
-the reference's image path lives in ``pylops`` (Convolve2D, Gradient) and
-``pyproximal`` (L2, L1, L21, TV), which are neither vendored in /root/reference,
-nor pinned to a version (README.md:5 ``pip install -U``), nor installed or
-installable in this image.  The classes below restate their published behaviour as
-frozen in SURVEY.md section 8(a) rows I1-I5; each rule is one small named function so
-it can be corrected if the libraries become available.  What IS pinned:
+The per-iteration arithmetic of the reference's image path lives in ``pylops`` (Convolve2D, Gradient) and
+``pyproximal`` (L2, L1, L21, TV, AdaptivePrimalDual), which are neither vendored in /root/reference, nor pinned to
+a version (README.md:5 ``pip install -U``), nor installed or installable in this image.  The classes below restate
+their published behaviour, each rule one small named function.  PARITY PINNED against results the reference itself
+holds: the per-sample SNR / PSNR / MSE curves of its committed figures
+fig/fig_prox_lmc_deconv_einstein_{MYULA,ULPDA,MAP}_1000_snr_psnr_mse.pdf, digitised by oracle/digitise_figs.py into
+tests/golden/deconv_curves.npz (2.2e-7 dB per vertex) and reproduced by this module on fig/einstein.png with the
+reference's noise stream to <= 1e-7 dB (tests/test_oracle_pinned.py; the CUDA path: tests/test_pinned_gpu.py).
 
-* the sampler loops and ``L2_ncvx_tv`` follow the reference's own source line by
-  line (algs.py:22-291, 295-474, 477-587);
-* the LSQR solve is executed by ``scipy.sparse.linalg.lsqr`` itself -- the very
-  function the reference calls (algs.py:250, pyproximal ``L2.prox``) -- and the blur
-  by ``scipy.signal.convolve/correlate`` (what ``Convolve2D`` reduces to);
-* operator identities (adjoint dot-tests, Moreau identity, prox optimality) are
-  checked in tests/test_oracle_deconv.py.
+* the sampler loops and ``L2_ncvx_tv`` follow the reference's own source line by line (algs.py:22-291, 295-474,
+  477-587);
+* the LSQR solve is executed by ``scipy.sparse.linalg.lsqr`` itself -- the very function the reference calls
+  (algs.py:250, pyproximal ``L2.prox``) -- and the blur by ``scipy.signal.convolve/correlate`` (what ``Convolve2D``
+  reduces to);
+* operator identities (adjoint dot-tests, Moreau identity, prox optimality) are checked in
+  tests/test_oracle_deconv.py.
 
-Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline /
-``--impl reference`` leg may import this module; the product path never does.
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline / ``--impl reference`` leg may import
+this module; the product path never does.
 """
 from __future__ import annotations
 

@@ -38,8 +38,16 @@ def loops(cubin, pattern):
             m = re.search(r"\bBRA\b.*0x([0-9a-f]+)", t)
             if m and int(m.group(1), 16) < a:
                 tgt = int(m.group(1), 16)
-                found.append([x for b, x in ins if tgt <= b <= a])
-        yield fn, sorted(found, key=len)
+                body = [(b, x) for b, x in ins if tgt <= b <= a]
+                # blocks skipped by a predicated FORWARD branch inside the loop (here: the shifted re-evaluation taken
+                # only when every mixture component underflows) are reported apart from the steady-state path
+                cold = set()
+                for b, x in body:
+                    f = re.search(r"^@!?U?P\d+\s+BRA\b.*0x([0-9a-f]+)", x)
+                    if f and b < int(f.group(1), 16) <= a:
+                        cold.update(c for c, _ in body if b < c < int(f.group(1), 16))
+                found.append(([x for b, x in body if b not in cold], [x for b, x in body if b in cold]))
+        yield fn, sorted(found, key=lambda hc: len(hc[0]) + len(hc[1]))
 
 
 def census(body):
@@ -55,9 +63,10 @@ if __name__ == "__main__":
     cubin = cubin_of(sys.argv[1])
     for fn, ls in loops(cubin, sys.argv[2]):
         print(fn)
-        for body in ls[:int(sys.argv[3]) if len(sys.argv) > 3 else 2]:
+        for body, cold in ls[:int(sys.argv[3]) if len(sys.argv) > 3 else 2]:
             cnt, packed = census(body)
             n = len(body)
-            print(f"  loop of {n} instructions: packed {packed} ({packed / n:.3f}), MUFU {cnt['MUFU']}, "
-                  f"IMAD {cnt['IMAD']}, dispatch slots (packed x2) {n + packed}")
+            print(f"  loop: {n} instructions on the steady-state path (+{len(cold)} in forward-branch-skipped blocks): "
+                  f"packed {packed} ({packed / n:.3f}), MUFU {cnt['MUFU']}, IMAD {cnt['IMAD']}, "
+                  f"dispatch slots (packed x2) {n + packed}")
             print("   ", dict(cnt.most_common(16)))

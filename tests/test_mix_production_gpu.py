@@ -172,3 +172,23 @@ def test_mixture_weights_recovered():
     assert np.isfinite(th).all()
     d = np.min(np.stack([np.linalg.norm(th - m, axis=1) for m in z["mus"]]), axis=0)
     assert np.quantile(d, 0.99) < 4.0
+
+
+@pytest.mark.parametrize("which,alg", [("laplace", "ula"), ("laplace", "mala"), ("gauss", "ula"), ("prox", "myula")])
+def test_far_start_takes_the_shifted_fallback(which, alg):
+    """fp32 production evaluates the mixture without the log-sum-exp shift and falls back to the shifted form when
+    every component underflows (mix_kernels.cu, eval_laplace / eval_gauss): chains started ~600 units from all modes
+    must stay finite and move towards the modes exactly as the fp64 kernel does."""
+    import torch
+    z, s, _ = make_samplers()[which]
+    kw, _ = alg_params(z, alg)
+    far = {"laplace": 600.0, "gauss": 40.0, "prox": 40.0}[which]     # Gaussian tails underflow much sooner
+    th0 = np.tile(np.array([[far, -far]]), (128, 1)) + np.arange(128)[:, None] * 0.01
+    K = 30
+    a = s.sample_chains(alg, float(z["gamma"]), chains=128, K=K, dtype="float32", seed=3, theta0=th0, **kw)
+    b = s.sample_chains(alg, float(z["gamma"]), chains=128, K=K, dtype="float64", seed=3, theta0=th0, **kw)
+    ta, tb = a.theta.double().cpu().numpy(), b.theta.double().cpu().numpy()
+    assert np.isfinite(ta).all() and np.isfinite(a.sum1).all()
+    assert np.abs(ta).max() < far + 10          # did not blow up
+    # same direction and size of the drift as the fp64 chain (different Philox normals: fp32 takes 24-bit uniforms)
+    assert np.abs((ta - th0).mean(axis=0) - (tb - th0).mean(axis=0)).max() < 0.05 * max(1.0, np.abs(tb - th0).max())
