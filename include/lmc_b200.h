@@ -170,6 +170,21 @@ typedef struct lmc_img_ulpda_params {
   double lsqr_atol, lsqr_btol, lsqr_conlim;   /* scipy lsqr defaults 1e-6, 1e-6, 1e8 */
 } lmc_img_ulpda_params;
 
+/* Non-convex data term of the reference, algs.L2_ncvx_tv (algs.py:22-291): f(x) = sigma/2 ||Hx - b||^2 - lamda *
+ * env_gamma(TV)(x), evaluated INSIDE the sampler kernels for all N iterations of a launch.
+ * kind 1 = MC-TV (Op2 = Gradient): grad_moreau = G^T(w(Gx) Gx), isotropic w = min(1/gamma, 1/|Gx|_2) (|Gx| = 0 read as
+ *          1e-9), anisotropic w Gx = (Gx - soft(Gx, gamma)) / gamma   (algs.py:211-217, 271-277);
+ * kind 2 = ME-TV (Op2 = None, isotropic): grad_moreau = (x - TV(dims, 1., niter, rtol).prox(x, gamma)) / gamma
+ *          (algs.py:169, 221-223, 280-282): the kernel runs the inner TV prox with its own TV machinery.
+ * MYULA: grad f(x) = sigma H^T(Hx - b) - lamda grad_moreau(x)  (algs.py:283-291). */
+typedef struct lmc_img_ncvx {
+  int32_t kind;             /* 0 none, 1 MC-TV, 2 ME-TV */
+  int32_t isotropic;
+  double lamda, gamma;
+  int32_t niter;            /* ME-TV: inner TV iterations (the driver's niter_l2 = 50) */
+  double rtol;              /* ME-TV: inner TV rtol (1e-4) */
+} lmc_img_ncvx;
+
 /* Buffers of one run of C image chains x N sampler iterations.  NULL = not requested. */
 typedef struct lmc_img_io {
   void* d_x;                /* (C,P) in/out sampler state */
@@ -196,6 +211,8 @@ typedef struct lmc_img_io {
   const void* d_fgrad_extra; /* (C,P) MYULA: grad f(x) = sigma H^T(Hx - b) + fgrad_scale * this  (algs.py:283-291) */
   double fgrad_scale;        /* -lamda */
   const void* d_prox_arg;    /* (C,P) ULPDA: replaces x - tau (G^T y + z) as the argument of the L2 prox (algs.py:224-256) */
+  const lmc_img_ncvx* ncvx;  /* HOST pointer or NULL: non-convex term evaluated in-kernel, any N (MYULA streaming / band
+                                kernels); excludes d_fgrad_extra */
 } lmc_img_io;
 
 size_t lmc_img_myula_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C);

@@ -82,13 +82,19 @@ class ImgUlpdaParams(C.Structure):
                 ("lsqr_conlim", C.c_double)]
 
 
+class ImgNcvx(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("isotropic", C.c_int32), ("lamda", C.c_double), ("gamma", C.c_double),
+                ("niter", C.c_int32), ("rtol", C.c_double)]
+
+
 class ImgIo(C.Structure):
     _fields_ = [("d_x", C.c_void_p), ("d_y", C.c_void_p), ("d_xhat", C.c_void_p), ("d_warm", C.c_void_p),
                 ("d_z", C.c_void_p), ("d_noise", C.c_void_p), ("d_samples", C.c_void_p),
                 ("d_ysamples", C.c_void_p), ("d_mean", C.c_void_p), ("d_m2", C.c_void_p),
                 ("d_counters", C.c_void_p), ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
                 ("burnin", C.c_int64), ("stat_count0", C.c_int64), ("iter_offset", C.c_uint64),
-                ("d_fgrad_extra", C.c_void_p), ("fgrad_scale", C.c_double), ("d_prox_arg", C.c_void_p)]
+                ("d_fgrad_extra", C.c_void_p), ("fgrad_scale", C.c_double), ("d_prox_arg", C.c_void_p),
+                ("ncvx", C.POINTER(ImgNcvx))]
 
 
 # name -> (restype, argtypes); must list every symbol include/lmc_b200.h declares

@@ -10,7 +10,8 @@ size_t myula_ws_bytes(int ny, int nx, long long C) {
   const size_t bands = (size_t)(ny + MB_RB - 1) / MB_RB;   // the band kernel keeps one partial per band
   if (bands > tiles) tiles = bands;
   return 256 /* n_active + counters */ + align_up(C * sizeof(TvState)) + align_up(C * tiles * sizeof(double)) +
-         align_up((size_t)C * P * sizeof(real)) /* grad */ + align_up((size_t)6 * C * P * sizeof(real)) /* duals */;
+         align_up((size_t)C * P * sizeof(real)) /* grad */ + align_up((size_t)6 * C * P * sizeof(real)) /* duals */ +
+         align_up((size_t)C * P * sizeof(real)) /* Moreau-envelope gradient of an in-kernel non-convex term */;
 }
 
 // the band kernel covers the H5 / H6 / H7 blurs of the driver; two image columns per thread on even widths (the
@@ -23,7 +24,7 @@ bool myula_band_ok(const lmc_img_problem* pb) {
 }
 
 template <typename real, int NT, int GW, int TW = 2>
-int launch_myula_band(MyulaArgs<real>& A, cudaStream_t st) {
+int launch_myula_band(MyulaArgs<real>& A, const MyulaArgs<real>& B, cudaStream_t st) {
   const size_t smem = myula_band_smem_bytes<real, NT>(A.pitch);
   auto kern = img_myula_band_kernel<real, NT, GW, TW>;
   int dev = 0, sms = 0, occ = 0;
@@ -36,7 +37,7 @@ int launch_myula_band(MyulaArgs<real>& A, cudaStream_t st) {
   LMC_REQUIRE(items < (1ll << 31) && A.g.P < (1ll << 31), "MYULA band kernel: 32-bit item / pixel indices exceeded");
   int grid = (int)(items < cap ? items : cap);
   if (grid < 1) grid = 1;
-  void* kargs[] = {(void*)&A};
+  void* kargs[] = {(void*)&A, (void*)&B};
   LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(BAND_BT), kargs, smem, st));
   return 0;
 }
@@ -45,8 +46,10 @@ template <typename real>
 int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long long C, long long N, uint64_t seed,
               uint64_t chain_offset, const lmc_img_io* io, int mode, const void* tv_in, void* tv_out,
               cudaStream_t st, bool band = false) {
-  MyulaArgs<real> A;
+  MyulaArgs<real> A, B;
   memset(&A, 0, sizeof(A));
+  memset(&B, 0, sizeof(B));
+  B.mode = -1;
   fill_geom(pb, A.g);
   if (band) {   // one objective partial per band of MB_RB rows
     A.g.tiles_x = 1;
@@ -69,6 +72,8 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
   A.grad = (real*)ws;
   ws += align_up((size_t)C * A.g.P * sizeof(real));
   A.D = (real*)ws;
+  ws += align_up((size_t)6 * C * A.g.P * sizeof(real));
+  A.gextra_w = (real*)ws;
   A.counters = io->d_counters ? io->d_counters : local_counters;
   A.C = C;
   A.N = N;
@@ -99,6 +104,33 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
     A.s2t = (real)sqrt(2 * pr->tau);
     A.tv_gamma = (real)(pr->tv_sigma * (pr->epsg * pr->gamma));   // TV.prox(x, epsg*gamma): sigma * tau
     A.tv_objw = (double)A.tv_gamma * pr->tv_sigma;                 // obj = .5|x-sol|^2 + gamma * TV.__call__(sol)
+    // non-convex data term evaluated in-kernel (algs.L2_ncvx_tv, algs.py:270-291): grad f = sigma H^T(Hx - b)
+    // - lamda * grad_moreau(x), for all N iterations of the launch
+    if (io->ncvx != nullptr && io->ncvx->kind != 0) {
+      const lmc_img_ncvx& nc = *io->ncvx;
+      A.gextra = A.gextra_w;
+      A.gscale = (real)(-nc.lamda);
+      if (nc.kind == 1) {          // MC-TV: 7-point stencil in phase G
+        A.nc.kind = 1;
+        A.nc.W.inv_gamma = (real)(1.0 / nc.gamma);
+        A.nc.W.gamma = (real)nc.gamma;
+        A.nc.W.iso = nc.isotropic;
+        A.nc.post_div = (real)(nc.isotropic ? 1.0 : nc.gamma);
+      } else {                     // ME-TV: prelude B = TV(dims, 1., niter, rtol).prox(x, gamma), out = (x - prox)/gamma
+        B = A;
+        B.mode = 2;
+        B.nc.kind = 0;
+        B.gextra = nullptr;
+        B.out = A.gextra_w;
+        B.me_den = (real)nc.gamma;
+        B.tv_gamma = (real)nc.gamma;                  // sigma (1) * tau (gamma)
+        B.tv_objw = (double)B.tv_gamma * 1.0;
+        B.tv_passes = nc.niter + LMC_TV_EXTRA_PASS;
+        B.tv_rtol = nc.rtol;
+        B.counters = local_counters + 4;              // inner sweeps are not the sampler's TV sweeps
+        B.noise = nullptr; B.samples = nullptr; B.mean = nullptr; B.m2 = nullptr;
+      }
+    }
   } else {
     A.x = (real*)const_cast<void*>(tv_in);
     A.out = (real*)tv_out;
@@ -109,9 +141,9 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
   if (band) {
     if (pb->nx & 1) {   // odd width: rows are not pair-aligned, one column per thread in every phase
       switch (pb->ntap_y) {
-        case 5: return launch_myula_band<real, 5, 1, 1>(A, st);
-        case 6: return launch_myula_band<real, 6, 1, 1>(A, st);
-        default: return launch_myula_band<real, 7, 1, 1>(A, st);
+        case 5: return launch_myula_band<real, 5, 1, 1>(A, B, st);
+        case 6: return launch_myula_band<real, 6, 1, 1>(A, B, st);
+        default: return launch_myula_band<real, 7, 1, 1>(A, B, st);
       }
     }
     const void* ptrs[] = {A.x, A.b, A.grad, A.D};
@@ -120,12 +152,12 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
                   "MYULA band kernel: buffers must be aligned to two elements");
     // two columns per thread in the gradient phase when the blur window is the driver's (BandWin)
     switch (pb->ntap_y) {
-      case 5: return pb->lo_x == BandWin<5>::LO ? launch_myula_band<real, 5, 2>(A, st) : launch_myula_band<real, 5, 1>(A, st);
-      case 6: return pb->lo_x == BandWin<6>::LO ? launch_myula_band<real, 6, 2>(A, st) : launch_myula_band<real, 6, 1>(A, st);
-      default: return pb->lo_x == BandWin<7>::LO ? launch_myula_band<real, 7, 2>(A, st) : launch_myula_band<real, 7, 1>(A, st);
+      case 5: return pb->lo_x == BandWin<5>::LO ? launch_myula_band<real, 5, 2>(A, B, st) : launch_myula_band<real, 5, 1>(A, B, st);
+      case 6: return pb->lo_x == BandWin<6>::LO ? launch_myula_band<real, 6, 2>(A, B, st) : launch_myula_band<real, 6, 1>(A, B, st);
+      default: return pb->lo_x == BandWin<7>::LO ? launch_myula_band<real, 7, 2>(A, B, st) : launch_myula_band<real, 7, 1>(A, B, st);
     }
   }
-  return launch_persistent(img_myula_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);
+  return launch_persistent(img_myula_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st, &B);
 }
 
 }  // namespace
@@ -150,6 +182,11 @@ extern "C" int lmc_img_myula_run(const lmc_img_problem* pb, const lmc_img_myula_
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_myula_run: b_chain_stride must be 0 or ny*nx");
   LMC_REQUIRE(io->d_fgrad_extra == nullptr || N == 1, "lmc_img_myula_run: d_fgrad_extra needs N == 1");
+  LMC_REQUIRE(io->ncvx == nullptr || io->ncvx->kind == 0 || io->d_fgrad_extra == nullptr,
+              "lmc_img_myula_run: ncvx and d_fgrad_extra are two ways to pass the same term");
+  LMC_REQUIRE(io->ncvx == nullptr || (io->ncvx->kind >= 0 && io->ncvx->kind <= 2 && (io->ncvx->kind == 0 ||
+              (io->ncvx->gamma > 0 && (io->ncvx->kind == 1 || (io->ncvx->isotropic && io->ncvx->niter >= 0))))),
+              "lmc_img_myula_run: bad ncvx descriptor (ME-TV needs isotropic = 1)");
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64 ? run_myula<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st)
                           : run_myula<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st);
@@ -180,6 +217,11 @@ extern "C" int lmc_img_myula_run_band(const lmc_img_problem* pb, const lmc_img_m
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_myula_run_band: b_chain_stride must be 0 or ny*nx");
   LMC_REQUIRE(io->d_fgrad_extra == nullptr || N == 1, "lmc_img_myula_run_band: d_fgrad_extra needs N == 1");
+  LMC_REQUIRE(io->ncvx == nullptr || io->ncvx->kind == 0 || io->d_fgrad_extra == nullptr,
+              "lmc_img_myula_run_band: ncvx and d_fgrad_extra are two ways to pass the same term");
+  LMC_REQUIRE(io->ncvx == nullptr || (io->ncvx->kind >= 0 && io->ncvx->kind <= 2 && (io->ncvx->kind == 0 ||
+              (io->ncvx->gamma > 0 && (io->ncvx->kind == 1 || (io->ncvx->isotropic && io->ncvx->niter >= 0))))),
+              "lmc_img_myula_run_band: bad ncvx descriptor (ME-TV needs isotropic = 1)");
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64 ? run_myula<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true)
                           : run_myula<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true);

@@ -41,9 +41,10 @@ inline void identity_problem(lmc_img_problem& pb, int ny, int nx) {
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
-// cooperative launch: one CTA per SM x occupancy, capped by the work items
+// cooperative launch: one CTA per SM x occupancy, capped by the work items; `args2` = optional second kernel argument
 template <typename Kern, typename Args>
-int launch_persistent(Kern kern, const Args& args, long long items, size_t smem, cudaStream_t st) {
+int launch_persistent(Kern kern, const Args& args, long long items, size_t smem, cudaStream_t st,
+                      const Args* args2 = nullptr) {
   int dev = 0, sms = 0, occ = 0, coop = 0;
   LMC_CUDA_OK(cudaGetDevice(&dev));
   LMC_CUDA_OK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
@@ -55,7 +56,7 @@ int launch_persistent(Kern kern, const Args& args, long long items, size_t smem,
   long long cap = (long long)sms * occ;
   int grid = (int)(items < cap ? items : cap);
   if (grid < 1) grid = 1;
-  void* kargs[] = {(void*)&args};
+  void* kargs[] = {(void*)&args, (void*)args2};
   LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(lmcimg::NTHREADS), kargs, smem, st));
   return 0;
 }

@@ -144,6 +144,16 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
 #pragma unroll
       for (int q = 0; q < GW; ++q) go.a[q] = A.sigma_l2 * gv.a[q];
       stp<real, GW>(gout + o, go);
+      if (A.nc.kind == 1) {   // MC-TV: 7-point stencil out of the staged band (halo rows E >= 1, zero pad columns)
+        P2 ge;
+#pragma unroll
+        for (int q = 0; q < GW; ++q) {
+          const real* xp = X + (k + E) * pitch + BAND_PAD + c + q;
+          ge.a[q] = mctv_at(A.nc.W, i, c + q, g.ny, g.nx, [&](int di, int dj) { return xp[di * pitch + dj]; }) /
+                    A.nc.post_div;
+        }
+        stp<real, GW>(A.gextra_w + chain * g.P + o, ge);
+      }
       // TV sweep 0: rr = ss = 0 -> sol = x, obj = gamma sum |grad x|, p_1 = proj(-grad x / (8 gamma))
       const real* xr = X + (k + E) * pitch + BAND_PAD + c;
       const P2 xv = ldp<real, GW>(xr), xd = ldp<real, GW>(xr + pitch);
@@ -180,7 +190,7 @@ __device__ void mband_tv_sweep(const MyulaArgs<real>& A, BandSched& sched, int i
   for (int w; (w = sched.next(items)) < items || (sched.end(), false);) {
     long long chain; int i0;
     band_of(g, w, 0, RB, chain, i0);
-    if (!A.st[chain].active) continue;
+    if (it > 0 && !A.st[chain].active) continue;   // it == 0: the standalone sweep 0 of a prox-only pipeline (mode 2)
     const real* xc = A.x + chain * g.P;
     real* pn = dual_ptr(A, (it + 1) % 3, 0, chain);
     real* qn = dual_ptr(A, (it + 1) % 3, 1, chain);
@@ -278,7 +288,7 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
   using P4 = Pack<real, 4>;
   bool vec = (g.nx % 4 == 0);
   {
-    const void* ptrs[] = {A.x, A.grad, A.gextra, A.noise, A.samples, A.mean, A.m2};
+    const void* ptrs[] = {A.x, A.grad, A.gextra, A.noise, A.samples, A.mean, A.m2, A.out};
     for (const void* p : ptrs) vec = vec && (reinterpret_cast<size_t>(p) % (4 * sizeof(real)) == 0);
   }
   sched.begin();
@@ -298,6 +308,20 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
         const int nq = min(4, g.nx - jb);
         const long long o = chain * g.P + (long long)i * g.nx + jb;
         const long long os = (chain * A.N + n) * g.P + (long long)i * g.nx + jb;
+        if (A.mode == 2) {   // ME-TV prelude: out = (x - prox) / gamma, nothing else
+          const P4 xv = mb_ld4(A.x + o, nq, vec);
+          P4 ov;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const real* rr = RR + (a + 1) * pitch + BAND_PAD + jb + k;
+            const real* ss = SS + (a + 1) * pitch + BAND_PAD + jb + k;
+            const real t = ((-rr[0] + rr[-pitch]) - ss[0]) + ss[-1];
+            const real sol = xv.a[k] - A.tv_gamma * (-t);
+            ov.a[k] = (xv.a[k] - sol) / A.me_den;
+          }
+          mb_st4(A.out + o, ov, nq, vec);
+          continue;
+        }
         const P4 xv = mb_ld4(A.x + o, nq, vec), gr0 = mb_ld4(A.grad + o, nq, vec);
         P4 ge, xi, mn, m2v;
         if (A.gextra != nullptr) ge = mb_ld4(A.gextra + o, nq, vec);
@@ -338,7 +362,31 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
 }
 
 template <typename real, int NT, int GW, int TW>
-__global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid_constant__ MyulaArgs<real> A) {
+__device__ __forceinline__ void myula_band_iteration(const MyulaArgs<real>& A, BandSched& sched, long long n, real* smem,
+                                                     double* red, cg::grid_group& grid) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
+  if (A.mode == 0) mband_grad_sweep0<real, NT, GW>(A, sched, smem, red);
+  else mband_tv_sweep<real, TW>(A, sched, 0, smem, red);   // prox-only pipeline: sweep 0 without the data term
+  grid.sync();
+  phase_tv_scalar(A, 0);
+  grid.sync();
+  for (int it = 1; it < A.tv_passes; ++it) {
+    if (*(volatile int*)A.n_active == 0) break;
+    grid.sync();   // everyone has read n_active before it is reset
+    if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
+    mband_tv_sweep<real, TW>(A, sched, it, smem, red);
+    grid.sync();
+    phase_tv_scalar(A, it);
+    grid.sync();
+  }
+  mband_update<real, TW>(A, sched, n, smem);
+  grid.sync();
+}
+
+// A = the sampler, B = the ME-TV prelude or disabled (see img_myula_kernel)
+template <typename real, int NT, int GW, int TW>
+__global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid_constant__ MyulaArgs<real> A,
+                                                                    const __grid_constant__ MyulaArgs<real> B) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
   __shared__ double red[2 * BAND_NW];
@@ -351,22 +399,8 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid
     smem[idx] = real(0);
   grid.sync();
   for (long long n = 0; n < A.N; ++n) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-    mband_grad_sweep0<real, NT, GW>(A, sched, smem, red);
-    grid.sync();
-    phase_tv_scalar(A, 0);
-    grid.sync();
-    for (int it = 1; it < A.tv_passes; ++it) {
-      if (*(volatile int*)A.n_active == 0) break;
-      grid.sync();   // everyone has read n_active before it is reset
-      if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-      mband_tv_sweep<real, TW>(A, sched, it, smem, red);
-      grid.sync();
-      phase_tv_scalar(A, it);
-      grid.sync();
-    }
-    mband_update<real, TW>(A, sched, n, smem);
-    grid.sync();
+    if (B.mode == 2) myula_band_iteration<real, NT, GW, TW>(B, sched, n, smem, red, grid);
+    myula_band_iteration<real, NT, GW, TW>(A, sched, n, smem, red, grid);
   }
 }
 

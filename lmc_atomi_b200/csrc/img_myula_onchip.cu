@@ -594,6 +594,8 @@ extern "C" int lmc_img_myula_run_onchip(const lmc_img_problem* pb, const lmc_img
               "(use lmc_img_myula_run)", OC_CL * 32, OC_W);
   LMC_REQUIRE(C >= 0 && N >= 0, "lmc_img_myula_run_onchip: negative C or N");
   LMC_REQUIRE(pr->tau > 0 && pr->gamma > 0, "lmc_img_myula_run_onchip: tau and gamma must be positive");
+  LMC_REQUIRE(io->ncvx == nullptr || io->ncvx->kind == 0,
+              "lmc_img_myula_run_onchip: non-convex data terms run on the band / streaming kernels");
   LMC_REQUIRE(pr->tv_niter >= 0 && pr->tv_sigma * pr->epsg * pr->gamma > 0,
               "lmc_img_myula_run_onchip: TV needs niter >= 0 and sigma*epsg*gamma > 0");
   if (C == 0 || N == 0) return 0;

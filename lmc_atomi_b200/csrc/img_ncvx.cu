@@ -5,32 +5,11 @@
 // result through lmc_img_io::d_fgrad_extra (MYULA) / d_prox_arg (ULPDA).  HBM-bound pointwise/stencil work:
 // one thread per pixel, neighbours served by L1/L2.
 #include "img_common.cuh"
+#include "img_ncvx.cuh"
 
 using namespace lmcimg;
 
 namespace {
-
-template <typename real>
-struct MctvW {
-  real inv_gamma, gamma;
-  int iso;
-  // weighted forward differences (v0, v1) of the pixel whose differences are (d0, d1)
-  __device__ __forceinline__ void operator()(real d0, real d1, real& v0, real& v1) const {
-    if (iso) {
-      real n = Math<real>::sqrt(d0 * d0 + d1 * d1);
-      n = (n != real(0)) ? n : real(1e-9);                       // algs.py:212,274
-      const real w = Math<real>::min(inv_gamma, real(1) / n);    // np.minimum(1/gamma, 1/|Gx|)
-      v0 = w * d0;
-      v1 = w * d1;
-    } else {
-      // Gx - L1(1).prox(Gx, gamma): the residual of the soft threshold
-      const real s0 = Math<real>::max(Math<real>::abs(d0) - gamma, real(0));
-      const real s1 = Math<real>::max(Math<real>::abs(d1) - gamma, real(0));
-      v0 = d0 - (d0 < real(0) ? -s0 : s0);
-      v1 = d1 - (d1 < real(0) ? -s1 : s1);
-    }
-  }
-};
 
 // out = base * x + scale * (G^T(w(Gx) Gx) / post_div); G = forward differences, last row/col zero
 template <typename real>
@@ -43,24 +22,7 @@ __global__ void img_mctv_grad_kernel(int ny, int nx, MctvW<real> W, real base, r
     const int i = (int)(o / nx), j = (int)(o - (long long)i * nx);
     const real* x = xin + chain * P;
     const real xc = x[o];
-    const bool hd = i < ny - 1, hr = j < nx - 1, hu = i >= 1, hl = j >= 1;
-    real v0c = 0, v1c = 0, v0u = 0, v1l = 0, dmy;
-    // differences at (i, j)
-    W(hd ? x[o + nx] - xc : real(0), hr ? x[o + 1] - xc : real(0), v0c, v1c);
-    if (hu) {   // axis-0 component at (i-1, j): needs both differences of that pixel
-      const real xu = x[o - nx];
-      W(xc - xu, hr ? x[o - nx + 1] - xu : real(0), v0u, dmy);
-    }
-    if (hl) {   // axis-1 component at (i, j-1)
-      const real xl = x[o - 1];
-      W(hd ? x[o + nx - 1] - xl : real(0), xc - xl, dmy, v1l);
-    }
-    // G^T in the accumulation order of pylops.Gradient.rmatvec (axis 0, then axis 1)
-    real acc = real(0);
-    if (hd) acc -= v0c;
-    if (hu) acc += v0u;
-    if (hr) acc -= v1c;
-    if (hl) acc += v1l;
+    const real acc = mctv_at(W, i, j, ny, nx, [&](int di, int dj) { return x[o + di * nx + dj]; });
     const real m = scale * (acc / post_div);
     out[t] = (base != real(0)) ? base * xc + m : m;
   }

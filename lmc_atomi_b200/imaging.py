@@ -180,6 +180,13 @@ class MoreauTerm:
         self.kind, self.lamda, self.gamma = kind, float(lamda), float(gamma)
         self.isotropic, self.niter, self.rtol = bool(isotropic), int(niter), float(rtol)
 
+    def descriptor(self):
+        """The C-ABI form (lmc_img_ncvx) handed to the sampler kernels for in-kernel evaluation."""
+        d = _lib.ImgNcvx()
+        d.kind, d.isotropic = (1 if self.kind == "mc" else 2), int(self.isotropic)
+        d.lamda, d.gamma, d.niter, d.rtol = self.lamda, self.gamma, self.niter, self.rtol
+        return d
+
 
 def moreau_apply(dims, x, term: MoreauTerm, tau=None, counters=None):
     """``tau is None``: grad_moreau(x) (algs.py:270-282).  Otherwise the in-place pre-step of
@@ -344,33 +351,18 @@ class DeconvEngine:
               engine="auto", ncvx=None):
         """Advances the (C,P) device tensor ``x`` in place by N MYULA iterations (algs.py:564-583).
 
-        ``ncvx``: a MoreauTerm makes the data term the reference's L2_ncvx_tv (MC-TV / ME-TV): every iteration
-        evaluates grad_moreau(x) with the unit kernels of csrc/img_ncvx.cu and hands it to a one-iteration
-        launch of the streaming kernel (grad f = sigma H^T(Hx - b) - lamda grad_moreau(x), algs.py:283-291)."""
-        if ncvx is None:
-            return self._myula_launch(x, N, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, noise,
-                                      samples, mean, m2, burnin, stat_count0, iter_offset, engine)
-        if engine == "onchip":
-            raise NotImplementedError("the on-chip MYULA kernel has no non-convex data term; use engine='stream'")
-        torch = self.torch
-        Cn = x.shape[0]
-        nz = self._noise(noise, Cn, N)
-        keep = None
-        for n in range(int(N)):
-            gm = moreau_apply(self.dims, x, ncvx, counters=None)
-            nzn = nz[:, n:n + 1].contiguous() if nz is not None else None
-            sn = torch.empty((Cn, 1, self.P), dtype=self.tdt, device=self.dev) if samples is not None else None
-            keep = self._myula_launch(x, 1, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, nzn, sn,
-                                      mean, m2, burnin, stat_count0 + _folded(burnin, iter_offset, n),
-                                      iter_offset + n, engine, fgrad_extra=gm, fgrad_scale=-ncvx.lamda)
-            torch.cuda.current_stream(self.dev).synchronize()   # gm / workspace lifetime
-            if samples is not None:
-                samples[:, n] = sn[:, 0]
-        return keep
+        ``ncvx``: a MoreauTerm makes the data term the reference's L2_ncvx_tv (MC-TV / ME-TV): the band / tile
+        kernels evaluate grad_moreau(x) in-kernel every iteration (MC-TV: a 7-point stencil in the gradient phase;
+        ME-TV: an inner TV prox with the kernel's own TV machinery), grad f = sigma H^T(Hx - b) - lamda grad_moreau(x)
+        (algs.py:283-291), so the N iterations stay one launch."""
+        if ncvx is not None and engine == "onchip":
+            raise NotImplementedError("the on-chip MYULA kernel has no non-convex data term; use engine='auto'")
+        return self._myula_launch(x, N, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, noise,
+                                  samples, mean, m2, burnin, stat_count0, iter_offset, engine, ncvx=ncvx)
 
     def _myula_launch(self, x, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, epsg=1.0, seed=0, chain_offset=0,
                       noise=None, samples=None, mean=None, m2=None, burnin=0, stat_count0=0, iter_offset=0,
-                      engine="auto", fgrad_extra=None, fgrad_scale=0.0):
+                      engine="auto", fgrad_extra=None, fgrad_scale=0.0, ncvx=None):
         """One launch: N iterations of all chains.
 
         ``engine``: "onchip" = cluster kernel with the chain state in shared memory (fp32, images up to
@@ -384,7 +376,8 @@ class DeconvEngine:
         pr.tv_sigma, pr.tv_rtol, pr.tv_niter = float(tv_sigma), float(tv_rtol), int(tv_niter)
         if engine not in ("auto", "onchip", "band", "stream"):
             raise ValueError("engine must be 'auto', 'onchip', 'band' or 'stream'")
-        onchip = engine == "onchip" or (engine == "auto" and self.onchip_supported() and fgrad_extra is None)
+        onchip = engine == "onchip" or (engine == "auto" and self.onchip_supported() and fgrad_extra is None
+                                        and ncvx is None)
         band = engine == "band" or (engine == "auto" and not onchip and self.myula_band_supported())
         if onchip:
             ws = torch.empty(256, dtype=torch.uint8, device=self.dev)
@@ -396,6 +389,9 @@ class DeconvEngine:
         io.d_x = x.data_ptr()
         if fgrad_extra is not None:
             io.d_fgrad_extra, io.fgrad_scale = fgrad_extra.data_ptr(), float(fgrad_scale)
+        nc = ncvx.descriptor() if ncvx is not None else None
+        if nc is not None:
+            io.ncvx = C.pointer(nc)
         pb = self._problem()
         fn, name = ((lib.lmc_img_myula_run_onchip, "lmc_img_myula_run_onchip") if onchip
                     else (lib.lmc_img_myula_run_band, "lmc_img_myula_run_band") if band

@@ -108,3 +108,50 @@ def test_fp32_engine_with_moreau_term_tracks_fp64():
         torch.cuda.synchronize()
         outs.append(x.double().cpu().numpy())
     assert rel(outs[0], outs[1]) < 2e-4
+
+
+@pytest.mark.parametrize("engine", ["stream", "band"])
+@pytest.mark.parametrize("which,k,dims", [("mc", 5, (40, 36)), ("me", 5, (40, 36)), ("mc", 6, (33, 45)), ("me", 7, (48, 64))])
+def test_myula_nonconvex_in_kernel_multi_iteration_launch(which, k, dims, engine):
+    """The MC-TV stencil / ME-TV inner prox evaluated INSIDE the MYULA kernels (lmc_img_io::ncvx): one launch of N
+    iterations, band and tile kernels, against the oracle's L2_ncvx_tv on the reference noise stream (fp64)."""
+    import torch
+    from lmc_atomi_b200 import imaging as I
+    N = 7
+    D, compat, algs, pb, mc, me = _setup(dims, k)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(5, N, P)
+    want = D.MoreauYosidaUnadjustedLangevin(pb["l2_" + which](), pb["tv"](), pb["x0"], tau=pb["tau_myula"],
+                                            gamma=pb["gamma_myula"], niter=N, noise=noise)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    term = I.MoreauTerm(which, 0.3, 15.0, True, 50, 1e-4)
+    x = torch.zeros((1, P), dtype=torch.float64, device="cuda")
+    samples = torch.empty((1, N, P), dtype=torch.float64, device="cuda")
+    eng.myula(x, N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise[None], samples=samples, ncvx=term,
+              engine=engine)
+    got = samples.cpu().numpy()[0]
+    errs = [rel(got[n], want[n]) for n in range(N)]
+    assert max(errs) < 1e-10, errs
+
+
+@pytest.mark.parametrize("which", ["mc", "me"])
+def test_myula_nonconvex_in_kernel_many_chains_fp32(which):
+    """fp32, more chains than a wave, Philox noise, running mean: band kernel == tile kernel, and both track fp64."""
+    import torch
+    from lmc_atomi_b200 import deconv_bench, imaging as I
+    dev = torch.device("cuda", 0)
+    dims, N, Cn = (64, 96), 4, 40
+    term = I.MoreauTerm(which, 0.3, 15.0, True, 50, 1e-4)
+    out = {}
+    for dt, engine in (("float32", "band"), ("float32", "stream"), ("float64", "band")):
+        _, eng = deconv_bench.make_engine(dims, dev, dt)
+        noise = I.philox_image_noise(dims, Cn, N, seed=7, dtype="float64", device=dev).to(eng.tdt)
+        x = torch.zeros((Cn, dims[0] * dims[1]), dtype=eng.tdt, device=dev)
+        mean = torch.zeros_like(x)
+        eng.myula(x, N, 0.1125, 0.5625, 0.3, 10, 1e-4, noise=noise, mean=mean, ncvx=term, engine=engine)
+        torch.cuda.synchronize()
+        out[(dt, engine)] = (x.double().cpu().numpy(), mean.double().cpu().numpy())
+    for a, b in zip(out[("float32", "band")], out[("float32", "stream")]):
+        assert rel(a, b) < 1e-5
+    for a, b in zip(out[("float32", "band")], out[("float64", "band")]):
+        assert rel(a, b) < 2e-5
