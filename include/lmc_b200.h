@@ -176,7 +176,9 @@ typedef struct lmc_img_ulpda_params {
  *          1e-9), anisotropic w Gx = (Gx - soft(Gx, gamma)) / gamma   (algs.py:211-217, 271-277);
  * kind 2 = ME-TV (Op2 = None, isotropic): grad_moreau = (x - TV(dims, 1., niter, rtol).prox(x, gamma)) / gamma
  *          (algs.py:169, 221-223, 280-282): the kernel runs the inner TV prox with its own TV machinery.
- * MYULA: grad f(x) = sigma H^T(Hx - b) - lamda grad_moreau(x)  (algs.py:283-291). */
+ * MYULA: grad f(x) = sigma H^T(Hx - b) - lamda grad_moreau(x)  (algs.py:283-291).
+ * ULPDA: the argument of the L2 prox gets the in-place pre-step of L2_ncvx_tv.prox, arg += tau lamda grad_moreau(arg)
+ *        with the reference's grouping of the scalars (algs.py:208-223); both gfirst orders. */
 typedef struct lmc_img_ncvx {
   int32_t kind;             /* 0 none, 1 MC-TV, 2 ME-TV */
   int32_t isotropic;
@@ -211,12 +213,16 @@ typedef struct lmc_img_io {
   const void* d_fgrad_extra; /* (C,P) MYULA: grad f(x) = sigma H^T(Hx - b) + fgrad_scale * this  (algs.py:283-291) */
   double fgrad_scale;        /* -lamda */
   const void* d_prox_arg;    /* (C,P) ULPDA: replaces x - tau (G^T y + z) as the argument of the L2 prox (algs.py:224-256) */
-  const lmc_img_ncvx* ncvx;  /* HOST pointer or NULL: non-convex term evaluated in-kernel, any N (MYULA streaming / band
-                                kernels); excludes d_fgrad_extra */
+  const lmc_img_ncvx* ncvx;  /* HOST pointer or NULL: non-convex term evaluated in-kernel, any N (streaming / band kernels
+                                of both samplers; ULPDA needs lmc_img_ulpda_workspace_bytes_ncvx); excludes
+                                d_fgrad_extra / d_prox_arg */
 } lmc_img_io;
 
 size_t lmc_img_myula_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C);
 size_t lmc_img_ulpda_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C);
+/* ... with a non-convex term evaluated in-kernel (io->ncvx, kind as in lmc_img_ncvx): adds the prox-argument buffers
+ * and, for ME-TV, the state of the inner TV pipeline */
+size_t lmc_img_ulpda_workspace_bytes_ncvx(int dtype, int32_t ny, int32_t nx, int64_t C, int32_t kind);
 
 /* C chains x N iterations in ONE persistent cooperative launch.  Chain c draws its
  * noise from Philox4x32-10 keyed by seed with counter (pixel-quad, iteration,

@@ -109,6 +109,7 @@ SIGNATURES = {
                                        C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lmc_img_myula_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int32, C.c_int32, C.c_int64]),
     "lmc_img_ulpda_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int32, C.c_int32, C.c_int64]),
+    "lmc_img_ulpda_workspace_bytes_ncvx": (C.c_size_t, [C.c_int, C.c_int32, C.c_int32, C.c_int64, C.c_int32]),
     "lmc_img_myula_run": (C.c_int, [C.POINTER(ImgProblem), C.POINTER(ImgMyulaParams), C.c_int, C.c_int64,
                                     C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(ImgIo), C.c_void_p]),
     "lmc_img_myula_onchip_supported": (C.c_int, [C.POINTER(ImgProblem), C.c_int]),

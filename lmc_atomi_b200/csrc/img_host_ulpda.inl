@@ -15,6 +15,20 @@ size_t ulpda_ws_bytes(int ny, int nx, long long C) {
          4 * align_up((size_t)C * P * sizeof(real)) /* optb, u, v, w */;
 }
 
+// extra workspace of an in-kernel non-convex data term: arg_w, arg2_w; ME-TV adds the state of the TV pipeline
+// (n_active, per-chain TvState, per-tile objective partials, three rotating dual pairs)
+template <typename real>
+size_t ulpda_ncvx_ws_bytes(int ny, int nx, long long C, int kind) {
+  if (kind == 0) return 0;
+  const size_t P = (size_t)ny * nx, arr = align_up((size_t)C * P * sizeof(real));
+  size_t n = 2 * arr;
+  if (kind == 2) {
+    const size_t tiles = (size_t)((ny + TH - 1) / TH) * ((nx + TW - 1) / TW);
+    n += 256 + align_up(C * sizeof(TvState)) + align_up((size_t)C * tiles * sizeof(double)) + 6 * arr;
+  }
+  return n;
+}
+
 template <typename real>
 bool band_supported(const lmc_img_problem* pb) {
   if (pb->ntap_y != pb->ntap_x || pb->ntap_y < 5 || pb->ntap_y > 7) return false;   // H5 / H6 / H7
@@ -35,8 +49,9 @@ bool band_pairs(const UlpdaArgs<real>& A) {
 }
 
 template <typename real, int NT, int W>
-int launch_band(UlpdaArgs<real>& A, cudaStream_t st) {
-  const size_t smem = Band<real, NT, BAND_RB>::smem_bytes(A.pitch);
+int launch_band(UlpdaArgs<real>& A, const MyulaArgs<real>& B, cudaStream_t st) {
+  size_t smem = Band<real, NT, BAND_RB>::smem_bytes(A.pitch);
+  if (B.mode == 3 && smem < (size_t)4 * RS * RS * sizeof(real)) smem = (size_t)4 * RS * RS * sizeof(real);   // tile TV phases
   auto kern = img_ulpda_band_kernel<real, NT, BAND_RB, W>;
   int dev = 0, sms = 0, occ = 0;
   LMC_CUDA_OK(cudaGetDevice(&dev));
@@ -50,7 +65,7 @@ int launch_band(UlpdaArgs<real>& A, cudaStream_t st) {
   LMC_REQUIRE(items < (1ll << 31) && A.g.P < (1ll << 31), "ULPDA band kernel: 32-bit item / pixel indices exceeded");
   int grid = (int)(items < cap ? items : cap);
   if (grid < 1) grid = 1;
-  void* kargs[] = {(void*)&A};
+  void* kargs[] = {(void*)&A, (void*)&B};
   LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(BAND_BT), kargs, smem, st));
   return 0;
 }
@@ -60,7 +75,10 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
               uint64_t chain_offset, const lmc_img_io* io, int mode, const void* prox_in, void* prox_out,
               cudaStream_t st, bool band = false, long long group = 0) {
   UlpdaArgs<real> A;
+  MyulaArgs<real> B;
   memset(&A, 0, sizeof(A));
+  memset(&B, 0, sizeof(B));
+  B.mode = -1;
   fill_geom(pb, A.g);
   if (band) {   // one partial per band of BAND_RB rows
     A.g.tiles_x = 1;
@@ -72,7 +90,8 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
     if (group <= 0) group = C;
     A.group = group < C ? group : C;
   }
-  const size_t need = ulpda_ws_bytes<real>(pb->ny, pb->nx, C);
+  const int nc_kind = (mode == 0 && io->ncvx != nullptr) ? io->ncvx->kind : 0;
+  const size_t need = ulpda_ws_bytes<real>(pb->ny, pb->nx, C) + ulpda_ncvx_ws_bytes<real>(pb->ny, pb->nx, C, nc_kind);
   LMC_REQUIRE(io->d_workspace != nullptr && io->workspace_bytes >= need, "image workspace too small (%zu < %zu)",
               io->workspace_bytes, need);
   char* ws = (char*)io->d_workspace;
@@ -90,6 +109,39 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
   A.v = (real*)ws; ws += arr;
   A.w = (real*)ws; ws += arr;
   A.counters = io->d_counters ? io->d_counters : local_counters;
+  if (nc_kind != 0) {   // algs.L2_ncvx_tv.prox evaluated in-kernel (algs.py:201-223)
+    const lmc_img_ncvx& nc = *io->ncvx;
+    A.arg_w = (real*)ws; ws += arr;
+    A.arg2_w = (real*)ws; ws += arr;
+    A.nc.kind = nc_kind;
+    A.nc.W.inv_gamma = (real)(1.0 / nc.gamma);
+    A.nc.W.gamma = (real)nc.gamma;
+    A.nc.W.iso = nc.isotropic;
+    A.nc.post_div = real(1);
+    // grouping of the scalars as the reference writes them: x += tau * lamda * m (isotropic),
+    // x += tau * lamda / gamma * m (anisotropic MC-TV and ME-TV)
+    A.nc_scale = (real)(nc.isotropic && nc_kind == 1 ? pr->tau * nc.lamda : pr->tau * nc.lamda / nc.gamma);
+    if (nc_kind == 2) {   // TV(dims, 1., niter, rtol).prox(arg, gamma) by the tile TV pipeline
+      fill_geom(pb, B.g);
+      B.mode = 3;
+      B.C = C;
+      B.N = N;
+      B.x = A.arg_w;
+      B.out = A.arg2_w;
+      B.me_scale = A.nc_scale;
+      B.tv_gamma = (real)nc.gamma;
+      B.tv_objw = (double)B.tv_gamma * 1.0;
+      B.tv_passes = nc.niter + LMC_TV_EXTRA_PASS;
+      B.tv_rtol = nc.rtol;
+      B.n_active = (int*)ws;
+      B.counters = (unsigned long long*)(ws + 64);
+      ws += 256;
+      B.st = (TvState*)ws; ws += align_up(C * sizeof(TvState));
+      B.partial = (double*)ws; ws += align_up((size_t)C * B.g.tiles * sizeof(double));
+      B.D = (real*)ws; ws += 6 * arr;
+      A.group = C;   // the TV pipeline advances all chains together
+    }
+  }
   A.C = C;
   A.N = N;
   A.mode = mode;
@@ -127,7 +179,7 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
     A.g_sigma = (real)pr->g_sigma;
     A.isotropic = pr->g_isotropic;
     A.gfirst = pr->gfirst;
-    A.in = (const real*)io->d_prox_arg;
+    A.in = nc_kind != 0 ? A.arg2_w : (const real*)io->d_prox_arg;
   } else {
     A.in = (const real*)prox_in;
     A.out = (real*)prox_out;
@@ -135,12 +187,27 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
   if (band) {
     switch (pb->ntap_y) {
-      case 5: return band_pairs(A) ? launch_band<real, 5, 2>(A, st) : launch_band<real, 5, 1>(A, st);
-      case 6: return band_pairs(A) ? launch_band<real, 6, 2>(A, st) : launch_band<real, 6, 1>(A, st);
-      default: return band_pairs(A) ? launch_band<real, 7, 2>(A, st) : launch_band<real, 7, 1>(A, st);
+      case 5: return band_pairs(A) ? launch_band<real, 5, 2>(A, B, st) : launch_band<real, 5, 1>(A, B, st);
+      case 6: return band_pairs(A) ? launch_band<real, 6, 2>(A, B, st) : launch_band<real, 6, 1>(A, B, st);
+      default: return band_pairs(A) ? launch_band<real, 7, 2>(A, B, st) : launch_band<real, 7, 1>(A, B, st);
     }
   }
-  return launch_persistent(img_ulpda_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st);
+  {   // the second kernel argument has its own type: launch by hand
+    int dev = 0, sms = 0, occ = 0;
+    const size_t smem = (size_t)(B.mode == 3 ? 4 : 3) * RS * RS * sizeof(real);
+    auto kern = img_ulpda_kernel<real>;
+    LMC_CUDA_OK(cudaGetDevice(&dev));
+    LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    LMC_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LMC_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NTHREADS, smem));
+    LMC_REQUIRE(occ >= 1, "ULPDA kernel does not fit on an SM (smem %zu)", smem);
+    const long long cap = (long long)sms * occ, items = C * A.g.tiles;
+    int grid = (int)(items < cap ? items : cap);
+    if (grid < 1) grid = 1;
+    void* kargs[] = {(void*)&A, (void*)&B};
+    LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(NTHREADS), kargs, smem, st));
+    return 0;
+  }
 }
 
 }  // namespace
@@ -148,6 +215,12 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
 extern "C" size_t lmc_img_ulpda_workspace_bytes(int dtype, int32_t ny, int32_t nx, int64_t C) {
   if (ny < 1 || nx < 1 || C < 1) return 256;
   return dtype == LMC_F64 ? ulpda_ws_bytes<double>(ny, nx, C) : ulpda_ws_bytes<float>(ny, nx, C);
+}
+
+extern "C" size_t lmc_img_ulpda_workspace_bytes_ncvx(int dtype, int32_t ny, int32_t nx, int64_t C, int32_t kind) {
+  if (ny < 1 || nx < 1 || C < 1) return 256;
+  return lmc_img_ulpda_workspace_bytes(dtype, ny, nx, C) +
+         (dtype == LMC_F64 ? ulpda_ncvx_ws_bytes<double>(ny, nx, C, kind) : ulpda_ncvx_ws_bytes<float>(ny, nx, C, kind));
 }
 
 extern "C" int lmc_img_ulpda_run(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, int dtype, int64_t C,
@@ -165,6 +238,11 @@ extern "C" int lmc_img_ulpda_run(const lmc_img_problem* pb, const lmc_img_ulpda_
               "lmc_img_ulpda_run: b_chain_stride must be 0 or ny*nx");
   LMC_REQUIRE(io->d_prox_arg == nullptr || (N == 1 && !pr->gfirst),
               "lmc_img_ulpda_run: d_prox_arg needs N == 1 and gfirst == 0");
+  LMC_REQUIRE(io->ncvx == nullptr || io->ncvx->kind == 0 || io->d_prox_arg == nullptr,
+              "lmc_img_ulpda_run: ncvx and d_prox_arg are two ways to pass the same term");
+  LMC_REQUIRE(io->ncvx == nullptr || (io->ncvx->kind >= 0 && io->ncvx->kind <= 2 && (io->ncvx->kind == 0 ||
+              (io->ncvx->gamma > 0 && (io->ncvx->kind == 1 || (io->ncvx->isotropic && io->ncvx->niter >= 0))))),
+              "lmc_img_ulpda_run: bad ncvx descriptor (ME-TV needs isotropic = 1)");
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64 ? run_ulpda<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st)
                           : run_ulpda<float>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st);
@@ -194,6 +272,11 @@ extern "C" int lmc_img_ulpda_run_band(const lmc_img_problem* pb, const lmc_img_u
               "lmc_img_ulpda_run_band: b_chain_stride must be 0 or ny*nx");
   LMC_REQUIRE(io->d_prox_arg == nullptr || (N == 1 && !pr->gfirst),
               "lmc_img_ulpda_run_band: d_prox_arg needs N == 1 and gfirst == 0");
+  LMC_REQUIRE(io->ncvx == nullptr || io->ncvx->kind == 0 || io->d_prox_arg == nullptr,
+              "lmc_img_ulpda_run_band: ncvx and d_prox_arg are two ways to pass the same term");
+  LMC_REQUIRE(io->ncvx == nullptr || (io->ncvx->kind >= 0 && io->ncvx->kind <= 2 && (io->ncvx->kind == 0 ||
+              (io->ncvx->gamma > 0 && (io->ncvx->kind == 1 || (io->ncvx->isotropic && io->ncvx->niter >= 0))))),
+              "lmc_img_ulpda_run_band: bad ncvx descriptor (ME-TV needs isotropic = 1)");
   cudaStream_t st = (cudaStream_t)stream;
   return dtype == LMC_F64
              ? run_ulpda<double>(pb, pr, C, N, seed, chain_offset, io, 0, nullptr, nullptr, st, true, group)

@@ -40,9 +40,11 @@ struct MyulaArgs {
   int tv_passes;     // executed passes of the TV loop at most: niter + LMC_TV_EXTRA_PASS (`while iter <= niter`)
   double tv_rtol;
   double tv_objw;    // weight of sum |grad sol| in the objective of the exit test: gamma * sigma_TV (see lmc_b200.h)
-  int mode;  // 0 = MYULA, 1 = TV prox only (out = prox_{tv_gamma TV}(x)), 2 = ME-TV prelude (out = (x - prox) / me_den),
-             // -1 = disabled (the second argument block of a launch without an ME-TV term)
-  real me_den;        // mode 2: gamma of the Moreau envelope (algs.py:221-223, 280-282)
+  int mode;  // 0 = MYULA, 1 = TV prox only (out = prox_{tv_gamma TV}(x)), 2 = ME-TV prelude of MYULA (out = (x - prox)
+             // / me_den), 3 = ME-TV prelude of ULPDA (out = x + me_scale (x - prox), the in-place pre-step of
+             // L2_ncvx_tv.prox, algs.py:221-223), -1 = disabled (second argument block of a launch without ME-TV)
+  real me_den;        // mode 2: gamma of the Moreau envelope (algs.py:280-282)
+  real me_scale;      // mode 3: tau * lamda / gamma
   NcvxK<real> nc;     // mode 0: in-kernel MC-TV term (kind 1): gextra_w <- G^T(w(Gx) Gx) / post_div in phase G
   real* gextra_w;     // (C,P) workspace the in-kernel non-convex terms write (read back through `gextra`)
   // band kernel only (img_myula_band.inl)
@@ -288,6 +290,10 @@ __device__ void phase_update(const MyulaArgs<real>& A, long long n, real* smem) 
         }
         if (A.mode == 2) {   // ME-TV: grad of the Moreau envelope (x - prox) / gamma  (img_metv_combine_kernel)
           A.out[chain * g.P + o] = (xv - sol) / A.me_den;
+          continue;
+        }
+        if (A.mode == 3) {   // ME-TV pre-step of the L2 prox: x + tau lamda / gamma (x - prox)  (img_metv_combine_kernel)
+          A.out[chain * g.P + o] = xv + A.me_scale * (xv - sol);
           continue;
         }
         real xi = (A.noise != nullptr) ? A.noise[(chain * A.N + n) * g.P + o] : z[k];

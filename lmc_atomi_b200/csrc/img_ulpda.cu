@@ -19,6 +19,7 @@
 // The normalisations u/beta, v/alfa are never materialised: each stored vector carries a
 // pending scale that the next reader applies (saves one sweep per normalisation).
 #include "img_common.cuh"
+#include "img_myula_tile.cuh"   // the TV pipeline (ME-TV prelude of a non-convex data term) + MC-TV stencil
 
 using namespace lmcimg;
 
@@ -64,6 +65,12 @@ struct UlpdaArgs {
   int isotropic, gfirst, iter_lim, warm_on;
   double atol, btol, ctol;
   int mode;  // 0 = ULPDA, 1 = L2 prox only
+  // non-convex data term evaluated in-kernel (algs.L2_ncvx_tv.prox, algs.py:201-223): every iteration
+  // arg_w = x - tau (G^T y + z); `in` = arg_w + nc_scale * grad-like term(arg_w)
+  NcvxK<real> nc;     // kind 1: MC-TV stencil on arg_w; kind 2: ME-TV (TV pipeline of the second kernel argument)
+  real nc_scale;      // MC-TV: tau lamda (isotropic) or tau lamda / gamma (anisotropic)
+  real* arg_w;        // (C,P) workspace
+  real* arg2_w;       // (C,P) workspace = `in` when nc.kind != 0
   // band kernel only (img_ulpda_band.inl)
   int pitch;        // shared-memory row pitch in elements
   int* queue;       // 4 work-queue counters (BandSched)
@@ -528,8 +535,61 @@ __device__ void phase_dual(const UlpdaArgs<real>& A, long long n, real* smem) {
   }
 }
 
+// ---------------------------------------------------------------- non-convex data term (algs.py:201-223)
+// arg_w = x - tau (G^T y + z) on chains [c_lo, c_hi): the argument ULPDA hands to proxf.prox (img_pd_arg_kernel)
 template <typename real>
-__global__ void __launch_bounds__(NTHREADS) img_ulpda_kernel(const __grid_constant__ UlpdaArgs<real> A) {
+__device__ void phase_ncvx_arg(const UlpdaArgs<real>& A, long long c_lo, long long c_hi) {
+  const Geom<real>& g = A.g;
+  const long long total = (c_hi - c_lo) * g.P;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const long long cl = t / g.P, o = t - cl * g.P, chain = c_lo + cl;
+    const int i = (int)(o / g.nx), j = (int)(o - (long long)i * g.nx);
+    const real* y0 = A.y + chain * 2 * g.P;
+    const real* y1 = y0 + g.P;
+    real acc = real(0);
+    if (i < g.ny - 1) acc -= y0[o];
+    if (i >= 1) acc += y0[o - g.nx];
+    if (j < g.nx - 1) acc -= y1[o];
+    if (j >= 1) acc += y1[o - 1];
+    if (A.zlin != nullptr) acc += A.zlin[o];
+    A.arg_w[chain * g.P + o] = A.x[chain * g.P + o] - A.tau * acc;
+  }
+}
+
+// MC-TV: arg2_w = arg_w + nc_scale * (G^T(w(G arg) G arg) / post_div)   (img_mctv_grad_kernel with base = 1)
+template <typename real>
+__device__ void phase_ncvx_mc(const UlpdaArgs<real>& A, long long c_lo, long long c_hi) {
+  const Geom<real>& g = A.g;
+  const long long total = (c_hi - c_lo) * g.P;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const long long cl = t / g.P, o = t - cl * g.P, chain = c_lo + cl;
+    const int i = (int)(o / g.nx), j = (int)(o - (long long)i * g.nx);
+    const real* x = A.arg_w + chain * g.P;
+    const real acc = mctv_at(A.nc.W, i, j, g.ny, g.nx, [&](int di, int dj) { return x[o + di * g.nx + dj]; });
+    const real m = A.nc_scale * (acc / A.nc.post_div);
+    A.arg2_w[chain * g.P + o] = real(1) * x[o] + m;
+  }
+}
+
+// the pre-step of L2_ncvx_tv.prox for chains [c_lo, c_hi) (ME-TV: all chains; B is the TV pipeline on arg_w)
+template <typename real>
+__device__ __forceinline__ void ncvx_prestep(const UlpdaArgs<real>& A, const MyulaArgs<real>& B, long long c_lo,
+                                             long long c_hi, long long n, real* smem, double* red,
+                                             cg::grid_group& grid) {
+  phase_ncvx_arg(A, c_lo, c_hi);
+  grid.sync();
+  if (A.nc.kind == 1) {
+    phase_ncvx_mc(A, c_lo, c_hi);
+    grid.sync();
+  } else {
+    myula_tile_iteration(B, n, smem, red, grid);   // arg2_w = arg_w + tau lamda / gamma (arg_w - TV_1.prox(arg_w, gamma))
+  }
+}
+
+// A = the sampler; B = the TV pipeline of an ME-TV term (mode 3) or disabled (mode -1)
+template <typename real>
+__global__ void __launch_bounds__(NTHREADS) img_ulpda_kernel(const __grid_constant__ UlpdaArgs<real> A,
+                                                             const __grid_constant__ MyulaArgs<real> B) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
   __shared__ double red[NTHREADS / 32];
@@ -541,6 +601,7 @@ __global__ void __launch_bounds__(NTHREADS) img_ulpda_kernel(const __grid_consta
       phase_dual(A, n, smem);
       grid.sync();
     }
+    if (A.nc.kind != 0) ncvx_prestep(A, B, 0, A.C, n, smem, red, grid);
     if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
     phase_primal_init(A, smem, red);
     grid.sync();

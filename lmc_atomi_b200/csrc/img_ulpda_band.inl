@@ -427,7 +427,8 @@ __device__ void band_dual(const UlpdaArgs<real>& A, BandSched& sched, long long 
 }
 
 template <typename real, int NT, int RB, int W>
-__global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid_constant__ UlpdaArgs<real> A) {
+__global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid_constant__ UlpdaArgs<real> A,
+                                                                    const __grid_constant__ MyulaArgs<real> B) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);
   __shared__ double red[2 * BAND_NW];
@@ -452,6 +453,14 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid
       if (A.mode == 0 && A.gfirst) {
         band_dual<real, RB>(A, sched, c_lo, c_hi, n);
         grid.sync();
+      }
+      if (A.nc.kind != 0) {   // non-convex data term: the prox argument of this iteration (ME-TV: group == C)
+        ncvx_prestep(A, B, c_lo, c_hi, n, smem, red, grid);
+        if (A.nc.kind == 2) {   // the tile TV phases used the whole dynamic shared memory: restore the zero pad columns
+          const int nz = (Band<real, NT, RB>::XROWS + Band<real, NT, RB>::TROWS) * A.pitch;
+          for (int idx = threadIdx.x; idx < nz; idx += BAND_BT) smem[idx] = real(0);
+          __syncthreads();
+        }
       }
       if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
       band_primal_init<real, NT, RB, W>(A, sched, c_lo, c_hi, smem, red, wx, wy);

@@ -139,7 +139,7 @@ def _pooled_mean(torch, mean):
 
 
 def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=250, dtype="float32", engine="auto",
-              e2e_groups=4):
+              e2e_groups=4, ncvx=None):
     import torch
     _, eng = make_engine(dims, dev, dtype)
     _, image_name = bench_image(dims)
@@ -153,7 +153,7 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=250, d
 
     def launch(c0=0, c1=chains, advance=True):
         state["keep"].append(eng.myula(x[c0:c1], iters, tau, gamma, TAU_REG, 10, 1e-4, seed=0, mean=mean[c0:c1],
-                                       iter_offset=state["it"],
+                                       ncvx=ncvx, iter_offset=state["it"],
                                        stat_count0=state["it"] if advance else 0, engine=engine,
                                        chain_offset=rank * chains + c0))
         del state["keep"][:-8]
@@ -186,8 +186,10 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=250, d
     bpp = roofline.myula_bytes_per_pixel(j, item)
     peaks = roofline.measured_peaks()
     rate = chains * iters / secs                      # chain-iters/s on this GPU
-    onchip = engine == "onchip" or (engine == "auto" and eng.onchip_supported())
+    onchip = engine == "onchip" or (engine == "auto" and eng.onchip_supported() and ncvx is None)
     band = not onchip and (engine == "band" or (engine == "auto" and eng.myula_band_supported()))
+    if ncvx is not None:     # + the Moreau-envelope gradient: written in phase G, read in phase U (MC-TV)
+        bpp += 2 * item
     if onchip:
         kernel = "img_myula_onchip_kernel<32,5,%d>" % (1 if dims == (256, 256) else 0)
         policy = ("chain state resident in the shared memory of an 8-CTA cluster for all iterations of a launch; "
@@ -198,8 +200,9 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=250, d
     else:
         kernel = ("img_myula_band_kernel<%s,5,2>" if band else "img_myula_kernel<%s>") % ("float" if item == 4 else "double")
         policy = "per-chain arrays total far more than the 126 MB L2"
-        roof = roofline.hbm_roofline(kernel, bpp * P, roofline.myula_band_min_bytes_per_pixel(j, item) * P, rate,
-                                     roofline.MYULA_BAND, band and dims == (512, 512) and item == 4)
+        roof = roofline.hbm_roofline(kernel, bpp * P, (roofline.myula_band_min_bytes_per_pixel(j, item) +
+                                                       (2 * item if ncvx is not None else 0)) * P, rate,
+                                     roofline.MYULA_BAND, band and dims == (512, 512) and item == 4 and ncvx is None)
     return {"metric": "myula_deconv_chain_iters_per_sec", "value": world * rate,
             "unit": "chain-iters/s", "n_gpus": world, "pooled_mean_finite": bool(torch.isfinite(pooled).all().item()),
             "pixel_iters_per_sec": world * rate * P, "dtype": dtype, "dims": list(dims), "image": image_name,
@@ -209,7 +212,7 @@ def run_myula(dev, steps=3, warmup=3, chains=1024, dims=(256, 256), iters=250, d
 
 
 def run_ulpda(dev, steps=3, warmup=2, chains=512, dims=(512, 512), iters=100, dtype="float32", engine="auto", group=0,
-              e2e_groups=4):
+              e2e_groups=4, ncvx=None, isotropic=True):
     import torch
     _, eng = make_engine(dims, dev, dtype)
     _, image_name = bench_image(dims)
@@ -223,7 +226,8 @@ def run_ulpda(dev, steps=3, warmup=2, chains=512, dims=(512, 512), iters=100, dt
 
     def launch(c0=0, c1=chains, advance=True):
         state["keep"].append(eng.ulpda(x[c0:c1], xhat[c0:c1], y[c0:c1], warm[c0:c1], iters, tau, mu, 1.0, TAU_REG,
-                                       True, False, 50, seed=0, mean=mean[c0:c1], iter_offset=state["it"],
+                                       isotropic, False, 50, seed=0, mean=mean[c0:c1], ncvx=ncvx,
+                                       iter_offset=state["it"],
                                        stat_count0=state["it"] if advance else 0, engine=engine, group=group,
                                        chain_offset=rank * chains + c0))
         del state["keep"][:-8]
@@ -254,11 +258,14 @@ def run_ulpda(dev, steps=3, warmup=2, chains=512, dims=(512, 512), iters=100, dt
     k = c["lsqr_iterations"] / max(1.0, float(c["lsqr_solves"]))
     item = 4 if dtype == "float32" else 8
     bpp = roofline.ulpda_bytes_per_pixel(k, item)
+    if ncvx is not None:     # + arg (write, read) and the pre-stepped argument (write, read)
+        bpp += 4 * item
     rate = chains * iters / secs
     band = engine == "band" or (engine == "auto" and eng.band_supported())
     kernel = ("img_ulpda_band_kernel<%s,5,16,2>" if band else "img_ulpda_kernel<%s>") % ("float" if item == 4 else "double")
-    roof = roofline.hbm_roofline(kernel, bpp * P, roofline.ulpda_band_min_bytes_per_pixel(k, item) * P, rate,
-                                 roofline.ULPDA_BAND, band and dims == (512, 512) and item == 4)
+    roof = roofline.hbm_roofline(kernel, bpp * P, (roofline.ulpda_band_min_bytes_per_pixel(k, item) +
+                                                   (4 * item if ncvx is not None else 0)) * P, rate,
+                                 roofline.ULPDA_BAND, band and dims == (512, 512) and item == 4 and ncvx is None)
     return {"metric": "ulpda_deconv_chain_iters_per_sec", "value": world * rate,
             "unit": "chain-iters/s", "n_gpus": world, "pooled_mean_finite": bool(torch.isfinite(pooled).all().item()),
             "pixel_iters_per_sec": world * rate * P, "dtype": dtype, "dims": list(dims), "image": image_name,
@@ -277,4 +284,19 @@ def run(dev, steps=3, warmup=3, **kw):
     out["band_kernel_512"] = {k: big[k] for k in ("value", "unit", "dims", "image", "chains", "iters_per_launch",
                                                    "ms_per_launch", "tv_sweeps_per_iter", "engine", "e2e", "roofline")}
     out["ulpda"] = run_ulpda(dev, steps=max(1, min(steps, 2)), warmup=1)
+    # non-convex data terms evaluated in-kernel (models M2 / M3 of prox_lmc_deconv.py:106-113, 541-703): MC-TV = a
+    # 7-point stencil, ME-TV = an inner TV prox of 50 iterations per sampler iteration
+    keys = ("value", "unit", "dims", "image", "chains", "iters_per_launch", "ms_per_launch", "engine", "roofline")
+    mc = imaging.MoreauTerm("mc", TAU_REG, 15.0, True)
+    me = imaging.MoreauTerm("me", TAU_REG, 15.0, True, 50, 1e-4)
+    nc = {}
+    r = run_myula(dev, steps=1, warmup=1, chains=256, dims=(512, 512), iters=20, engine="band", ncvx=mc)
+    nc["myula_mctv_M2"] = {k: r[k] for k in keys + ("tv_sweeps_per_iter",)}
+    r = run_myula(dev, steps=1, warmup=1, chains=64, dims=(512, 512), iters=5, engine="band", ncvx=me)
+    nc["myula_metv_M3"] = {k: r[k] for k in keys + ("tv_sweeps_per_iter",)}
+    nc["myula_metv_M3"]["roofline"]["note"] = ("the inner TV(dims, 1, 50).prox runs 51 more dual sweeps per iteration; "
+                                               "the algorithmic byte count above covers the outer sampler only")
+    r = run_ulpda(dev, steps=1, warmup=1, chains=128, dims=(512, 512), iters=10, ncvx=mc, isotropic=False)
+    nc["ulpda_mctv_M2"] = {k: r[k] for k in keys + ("lsqr_iters_per_solve",)}
+    out["ncvx"] = nc
     return out

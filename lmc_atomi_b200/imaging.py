@@ -409,41 +409,18 @@ class DeconvEngine:
               stat_count0=0, iter_offset=0, engine="auto", group=0, ncvx=None):
         """Advances (x, xhat, y, warm) in place by N ULPDA iterations (algs.py:432-467).
 
-        ``ncvx``: a MoreauTerm makes proxf the reference's L2_ncvx_tv: every iteration forms the primal argument
-        x - tau (G^T y + z), adds tau*lamda*grad_moreau of it (algs.py:208-223) with the unit kernels of
-        csrc/img_ncvx.cu and hands the result to a one-iteration launch (gfirst=False only)."""
-        if ncvx is None:
-            return self._ulpda_launch(x, xhat, y, warm, N, tau, mu, theta, g_sigma, isotropic, gfirst, lsqr_iter_lim,
-                                      warm_start, atol, btol, conlim, z, seed, chain_offset, noise, samples, ysamples,
-                                      mean, m2, burnin, stat_count0, iter_offset, engine, group)
-        if gfirst:
-            raise NotImplementedError("L2_ncvx_tv with gfirst=True has no CUDA path (the driver uses gfirst=False)")
-        torch = self.torch
-        Cn = x.shape[0]
-        nz = self._noise(noise, Cn, N)
-        zt = torch.as_tensor(z).to(self.dev, self.tdt).reshape(self.P).contiguous() if z is not None else None
-        keep = None
-        for n in range(int(N)):
-            arg = pd_arg(self.dims, x, y, tau, zt)
-            arg = moreau_apply(self.dims, arg, ncvx, tau=float(tau))
-            nzn = nz[:, n:n + 1].contiguous() if nz is not None else None
-            sn = torch.empty((Cn, 1, self.P), dtype=self.tdt, device=self.dev) if samples is not None else None
-            ysn = torch.empty((Cn, 1, 2, self.P), dtype=self.tdt, device=self.dev) if ysamples is not None else None
-            keep = self._ulpda_launch(x, xhat, y, warm, 1, tau, mu, theta, g_sigma, isotropic, False, lsqr_iter_lim,
-                                      warm_start, atol, btol, conlim, None, seed, chain_offset, nzn, sn, ysn, mean, m2,
-                                      burnin, stat_count0 + _folded(burnin, iter_offset, n), iter_offset + n, engine,
-                                      group, prox_arg=arg)
-            torch.cuda.current_stream(self.dev).synchronize()
-            if samples is not None:
-                samples[:, n] = sn[:, 0]
-            if ysamples is not None:
-                ysamples[:, n] = ysn[:, 0]
-        return keep
+        ``ncvx``: a MoreauTerm makes proxf the reference's L2_ncvx_tv: every iteration the kernel forms the primal
+        argument x - tau (G^T y + z) and adds tau*lamda*grad_moreau of it (algs.py:208-223) in-kernel (MC-TV: a
+        7-point stencil phase; ME-TV: the inner TV prox by the tile TV pipeline), so the N iterations stay one
+        launch; both gfirst orders."""
+        return self._ulpda_launch(x, xhat, y, warm, N, tau, mu, theta, g_sigma, isotropic, gfirst, lsqr_iter_lim,
+                                  warm_start, atol, btol, conlim, z, seed, chain_offset, noise, samples, ysamples,
+                                  mean, m2, burnin, stat_count0, iter_offset, engine, group, ncvx=ncvx)
 
     def _ulpda_launch(self, x, xhat, y, warm, N, tau, mu, theta=1.0, g_sigma=1.0, isotropic=True, gfirst=True,
                       lsqr_iter_lim=50, warm_start=True, atol=1e-6, btol=1e-6, conlim=1e8, z=None, seed=0,
                       chain_offset=0, noise=None, samples=None, ysamples=None, mean=None, m2=None, burnin=0,
-                      stat_count0=0, iter_offset=0, engine="auto", group=0, prox_arg=None):
+                      stat_count0=0, iter_offset=0, engine="auto", group=0, prox_arg=None, ncvx=None):
         """One launch: N iterations of all chains.
 
         ``engine``: "band" = row-band kernel (fused two-pass blur, chains advanced in L2-sized groups of
@@ -456,10 +433,14 @@ class DeconvEngine:
         pr.g_isotropic, pr.gfirst = int(bool(isotropic)), int(bool(gfirst))
         pr.lsqr_iter_lim, pr.warm = int(lsqr_iter_lim), int(bool(warm_start))
         pr.lsqr_atol, pr.lsqr_btol, pr.lsqr_conlim = float(atol), float(btol), float(conlim)
-        nb = lib.lmc_img_ulpda_workspace_bytes(_dt(self.dtype), self.dims[0], self.dims[1], Cn)
+        nc = ncvx.descriptor() if ncvx is not None else None
+        nb = (lib.lmc_img_ulpda_workspace_bytes(_dt(self.dtype), self.dims[0], self.dims[1], Cn) if nc is None else
+              lib.lmc_img_ulpda_workspace_bytes_ncvx(_dt(self.dtype), self.dims[0], self.dims[1], Cn, nc.kind))
         ws = torch.empty(nb, dtype=torch.uint8, device=self.dev)
         nz = self._noise(noise, Cn, N)
         io = self._io(Cn, N, nz, samples, mean, m2, burnin, stat_count0, iter_offset, ws)
+        if nc is not None:
+            io.ncvx = C.pointer(nc)
         io.d_x, io.d_xhat, io.d_y, io.d_warm = x.data_ptr(), xhat.data_ptr(), y.data_ptr(), warm.data_ptr()
         zt = None
         if z is not None:

@@ -86,9 +86,14 @@ def test_ulpda_with_nonconvex_data_term(which, k, iso):
                                                 mu=pb["mu0"], theta=1., niter=N, seed=1, gfirst=False, returny=True)
     assert rel(got, want) < 1e-9 and rel(gy, wy) < 1e-9
     assert mine.count == N and rel(mine.x0, ref.x0) < 1e-9
-    with pytest.raises(NotImplementedError):
-        algs.UnadjustedLangevinPrimalDual(mine, g, compat.Gradient(dims), pb["x0"], tau=pb["tau0"], mu=pb["mu0"],
-                                          niter=2, gfirst=True)
+    # gfirst=True (algs.py:435-441) with the non-convex term: in-kernel since r02
+    ref2 = pb["l2_" + which]()
+    want2 = D.UnadjustedLangevinPrimalDual(ref2, g_ref, pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], theta=1., niter=3,
+                                           seed=2, gfirst=True)
+    mine.x0, mine.count = None, 0
+    got2 = algs.UnadjustedLangevinPrimalDual(mine, g, compat.Gradient(dims), pb["x0"], tau=pb["tau0"], mu=pb["mu0"],
+                                             theta=1., niter=3, seed=2, gfirst=True)
+    assert rel(got2, want2) < 1e-9
 
 
 def test_fp32_engine_with_moreau_term_tracks_fp64():
@@ -155,3 +160,57 @@ def test_myula_nonconvex_in_kernel_many_chains_fp32(which):
         assert rel(a, b) < 1e-5
     for a, b in zip(out[("float32", "band")], out[("float64", "band")]):
         assert rel(a, b) < 2e-5
+
+
+@pytest.mark.parametrize("engine", ["tile", "band"])
+@pytest.mark.parametrize("which,k,dims,iso", [("mc", 5, (40, 36), True), ("me", 5, (40, 36), True),
+                                               ("mc", 6, (33, 45), False), ("me", 7, (48, 64), True)])
+def test_ulpda_nonconvex_in_kernel_multi_iteration_launch(which, k, dims, iso, engine):
+    """L2_ncvx_tv.prox's pre-step evaluated INSIDE the ULPDA kernels (lmc_img_io::ncvx): one launch of N iterations
+    on both kernels against the oracle (fp64, reference noise stream), with the prior the driver pairs with the term."""
+    import torch
+    from lmc_atomi_b200 import imaging as I
+    N = 6
+    D, compat, algs, pb, mc, me = _setup(dims, k)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(3, N, P)
+    ref = pb["l2_" + which]() if iso else D.L2_ncvx_tv(dims=dims, Op=pb["H"], Op2=pb["Gop"], b=pb["y"].ravel(),
+                                                       sigma=1 / 0.75 ** 2, lamda=0.3, gamma=15.0, isotropic=False,
+                                                       niter=50)
+    g_ref = pb["l1iso"]() if which == "me" else pb["l1"]()
+    want = D.UnadjustedLangevinPrimalDual(ref, g_ref, pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], theta=1., niter=N,
+                                          gfirst=False, noise=noise)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float64")
+    term = I.MoreauTerm(which, 0.3, 15.0, iso, 50, 1e-4)
+    z = lambda *s: torch.zeros(s, dtype=torch.float64, device="cuda")
+    x, xhat, y, warm, samples = z(1, P), z(1, P), z(1, 2, P), z(1, P), z(1, N, P)
+    eng.ulpda(x, xhat, y, warm, N, pb["tau0"], pb["mu0"], 1.0, 0.3, which == "me", False, 50, noise=noise[None],
+              samples=samples, ncvx=term, engine=engine)
+    got = samples.cpu().numpy()[0]
+    errs = [rel(got[n], want[n]) for n in range(N)]
+    assert max(errs) < 1e-9, errs
+
+
+@pytest.mark.parametrize("which", ["mc", "me"])
+def test_ulpda_nonconvex_in_kernel_many_chains(which):
+    """Several chains with their own Philox noise and running means: band == tile kernel (fp64), fp32 tracks fp64."""
+    import torch
+    from lmc_atomi_b200 import deconv_bench, imaging as I
+    dev = torch.device("cuda", 0)
+    dims, N, Cn = (64, 96), 3, 9
+    term = I.MoreauTerm(which, 0.3, 15.0, True, 50, 1e-4)
+    out = {}
+    for dt, engine in (("float64", "band"), ("float64", "tile"), ("float32", "band")):
+        _, eng = deconv_bench.make_engine(dims, dev, dt)
+        noise = I.philox_image_noise(dims, Cn, N, seed=7, dtype="float64", device=dev).to(eng.tdt)
+        z = lambda *s: torch.zeros(s, dtype=eng.tdt, device=dev)
+        x, xhat, y, warm, mean = z(Cn, dims[0] * dims[1]), z(Cn, dims[0] * dims[1]), z(Cn, 2, dims[0] * dims[1]), \
+            z(Cn, dims[0] * dims[1]), z(Cn, dims[0] * dims[1])
+        eng.ulpda(x, xhat, y, warm, N, 0.534375, 1.0, 1.0, 0.3, True, False, 50, noise=noise, mean=mean, ncvx=term,
+                  engine=engine)
+        torch.cuda.synchronize()
+        out[(dt, engine)] = (x.double().cpu().numpy(), mean.double().cpu().numpy())
+    for a, b in zip(out[("float64", "band")], out[("float64", "tile")]):
+        assert rel(a, b) < 1e-10
+    for a, b in zip(out[("float32", "band")], out[("float64", "band")]):
+        assert rel(a, b) < 2e-4
