@@ -140,12 +140,6 @@ def proxdual(v, sigma, isotropic=True):
     return v
 
 
-def _folded(burnin, iter_offset, n):
-    """Samples a chunked run starting at global iteration ``iter_offset`` has folded into the running mean before
-    its n-th iteration (lmc_img_io::stat_count0 counts the samples folded in BEFORE a launch)."""
-    return max(0, int(iter_offset) + int(n) - max(int(burnin), int(iter_offset)))
-
-
 def tv_prox(dims, x, gamma, niter=10, rtol=1e-4, counters=None, sigma=1.0):
     """pyproximal.TV(dims, sigma, niter, rtol).prox with sigma*tau = gamma on device tensors (C,P) or (P,).
     ``sigma`` enters only the objective of the early-exit test (gamma * sigma * sum |grad sol|, see lmc_b200.h)."""

@@ -3,8 +3,10 @@
 The reference measures its samplers with ``ot.emd2(a, b, ot.dist(Z1, Z[:k+1]))**.5`` between K true samples and
 chain prefixes (lmc.py:386-416, lmc_laplace.py:426-451), a CPU network simplex.  Here the same transport problem
 is solved on the device by ``lmc_w2_sinkhorn`` (log-domain Sinkhorn, epsilon scaling, fp64): an approximation
-whose distance to the exact EMD is controlled by ``eps`` (default 1e-3 in squared-distance units, which the
-GPU tests hold within 1e-3 of the exact linear programme on the reference's kind of point sets).
+whose distance to the exact EMD is controlled by ``eps`` (default 1e-3 in squared-distance units): the GPU tests
+hold it within 1e-3 of the exact linear programme on point sets up to 300 x 300 and, at the drivers' K = 5000,
+within 5.6e-4 of the exact assignment (equal-size uniform sets: scipy ``linear_sum_assignment``).  Only the final
+eps stage decides ``converged``; intermediate stages of the eps-scaling that reach ``max_iters`` are warm starts.
 No CPU path: without the CUDA library / a device the calls raise.
 """
 from __future__ import annotations
@@ -67,8 +69,9 @@ class SinkhornW2:
                                                 1 if warm_start else 0, self._ws.data_ptr(), self._ws.numel() * 8,
                                                 C.byref(res), st), "lmc_w2_sinkhorn")
         if not res.converged:
-            warnings.warn("lmc_w2_sinkhorn stopped at max_iters=%d with potential change %.3g > tol*eps: the value "
-                          "is an upper estimate" % (self.max_iters, res.err))
+            warnings.warn("lmc_w2_sinkhorn stopped at max_iters=%d with potential change %.3g > tol*eps at the final "
+                          "eps: the column marginals are not matched to tolerance (mass %.6f), so the value is "
+                          "neither an upper nor a lower bound of the exact EMD" % (self.max_iters, res.err, res.mass))
         self.last = {"cost": res.cost, "w2": res.w2, "eps": res.eps, "err": res.err, "mass": res.mass,
                      "iters": int(res.iters), "converged": bool(res.converged)}
         self.history.append(self.last)
