@@ -23,23 +23,22 @@ bool myula_band_ok(const lmc_img_problem* pb) {
   return myula_band_smem_bytes<real, 7>(band_pitch(pb->nx)) <= 200 * 1024;
 }
 
-template <typename real, int NT, int GW, int TW = 2>
-int launch_myula_band(MyulaArgs<real>& A, const MyulaArgs<real>& B, cudaStream_t st) {
-  const size_t smem = myula_band_smem_bytes<real, NT>(A.pitch);
-  auto kern = img_myula_band_kernel<real, NT, GW, TW>;
-  int dev = 0, sms = 0, occ = 0;
-  LMC_CUDA_OK(cudaGetDevice(&dev));
-  LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  LMC_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  LMC_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, BAND_BT, smem));
-  LMC_REQUIRE(occ >= 1, "MYULA band kernel does not fit on an SM (smem %zu)", smem);
-  const long long cap = (long long)sms * occ, items = A.C * A.g.tiles;
-  LMC_REQUIRE(items < (1ll << 31) && A.g.P < (1ll << 31), "MYULA band kernel: 32-bit item / pixel indices exceeded");
-  int grid = (int)(items < cap ? items : cap);
-  if (grid < 1) grid = 1;
-  void* kargs[] = {(void*)&A, (void*)&B};
-  LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(BAND_BT), kargs, smem, st));
-  return 0;
+// The band kernels are instantiated per tap count in their own translation units (img_myula_band{5,6,7}.cu, compiled
+// in parallel): (dtype, GW, TW, NC) are resolved there.  A / B are MyulaArgs<float|double> of this layout.
+}  // namespace
+int lmc_myula_band_launch_nt5(int dtype, const void* A, const void* B, int gw, int tw, cudaStream_t st);
+int lmc_myula_band_launch_nt6(int dtype, const void* A, const void* B, int gw, int tw, cudaStream_t st);
+int lmc_myula_band_launch_nt7(int dtype, const void* A, const void* B, int gw, int tw, cudaStream_t st);
+namespace {
+
+template <typename real>
+int launch_myula_band(int nt, const MyulaArgs<real>& A, const MyulaArgs<real>& B, int gw, int tw, cudaStream_t st) {
+  const int dtype = sizeof(real) == 8 ? LMC_F64 : LMC_F32;
+  switch (nt) {
+    case 5: return lmc_myula_band_launch_nt5(dtype, &A, &B, gw, tw, st);
+    case 6: return lmc_myula_band_launch_nt6(dtype, &A, &B, gw, tw, st);
+    default: return lmc_myula_band_launch_nt7(dtype, &A, &B, gw, tw, st);
+  }
 }
 
 template <typename real>
@@ -139,23 +138,15 @@ int run_myula(const lmc_img_problem* pb, const lmc_img_myula_params* pr, long lo
   }
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
   if (band) {
-    if (pb->nx & 1) {   // odd width: rows are not pair-aligned, one column per thread in every phase
-      switch (pb->ntap_y) {
-        case 5: return launch_myula_band<real, 5, 1, 1>(A, B, st);
-        case 6: return launch_myula_band<real, 6, 1, 1>(A, B, st);
-        default: return launch_myula_band<real, 7, 1, 1>(A, B, st);
-      }
-    }
+    if (pb->nx & 1)   // odd width: rows are not pair-aligned, one column per thread in every phase
+      return launch_myula_band<real>(pb->ntap_y, A, B, 1, 1, st);
     const void* ptrs[] = {A.x, A.b, A.grad, A.D};
     for (const void* p : ptrs)
       LMC_REQUIRE(reinterpret_cast<size_t>(p) % (2 * sizeof(real)) == 0,
                   "MYULA band kernel: buffers must be aligned to two elements");
     // two columns per thread in the gradient phase when the blur window is the driver's (BandWin)
-    switch (pb->ntap_y) {
-      case 5: return pb->lo_x == BandWin<5>::LO ? launch_myula_band<real, 5, 2>(A, B, st) : launch_myula_band<real, 5, 1>(A, B, st);
-      case 6: return pb->lo_x == BandWin<6>::LO ? launch_myula_band<real, 6, 2>(A, B, st) : launch_myula_band<real, 6, 1>(A, B, st);
-      default: return pb->lo_x == BandWin<7>::LO ? launch_myula_band<real, 7, 2>(A, B, st) : launch_myula_band<real, 7, 1>(A, B, st);
-    }
+    const int lo = pb->ntap_y == 7 ? BandWin<7>::LO : BandWin<5>::LO;
+    return launch_myula_band<real>(pb->ntap_y, A, B, pb->lo_x == lo ? 2 : 1, 2, st);
   }
   return launch_persistent(img_myula_kernel<real>, A, C * A.g.tiles, (size_t)3 * RS * RS * sizeof(real), st, &B);
 }

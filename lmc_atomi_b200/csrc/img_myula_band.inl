@@ -112,7 +112,7 @@ __device__ __forceinline__ void mband_dual_update(real rr, real ss, real dx, rea
 
 // ---------------------------------------------------------------- phase G (+ sweep 0)
 // GW = image columns per thread of this phase (2 when the blur's tap windows start on even columns, else 1)
-template <typename real, int NT, int GW>
+template <typename real, int NT, int GW, bool NC>
 __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, real* smem, double* red) {
   using P2 = Pack<real, GW>;
   constexpr int RB = MB_RB, E = NT - 1;
@@ -144,7 +144,7 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
 #pragma unroll
       for (int q = 0; q < GW; ++q) go.a[q] = A.sigma_l2 * gv.a[q];
       stp<real, GW>(gout + o, go);
-      if (A.nc.kind == 1) {   // MC-TV: 7-point stencil out of the staged band (halo rows E >= 1, zero pad columns)
+      if (NC && A.nc.kind == 1) {   // MC-TV: 7-point stencil out of the staged band (halo rows E >= 1, zero pad columns)
         P2 ge;
 #pragma unroll
         for (int q = 0; q < GW; ++q) {
@@ -274,7 +274,7 @@ __device__ __forceinline__ void mb_st4(real* p, const Pack<real, 4>& v, int n, b
 }
 
 // ---------------------------------------------------------------- phase U
-template <typename real, int TW>
+template <typename real, int TW, bool NC>
 __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long long n, real* smem) {
   constexpr int RB = MB_RB, HB = MB_HB;
   const Geom<real>& g = A.g;
@@ -308,7 +308,7 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
         const int nq = min(4, g.nx - jb);
         const long long o = chain * g.P + (long long)i * g.nx + jb;
         const long long os = (chain * A.N + n) * g.P + (long long)i * g.nx + jb;
-        if (A.mode == 2) {   // ME-TV prelude: out = (x - prox) / gamma, nothing else
+        if (NC && A.mode == 2) {   // ME-TV prelude: out = (x - prox) / gamma, nothing else
           const P4 xv = mb_ld4(A.x + o, nq, vec);
           P4 ov;
 #pragma unroll
@@ -361,11 +361,14 @@ __device__ void mband_update(const MyulaArgs<real>& A, BandSched& sched, long lo
   }
 }
 
-template <typename real, int NT, int GW, int TW>
+// NC = the launch carries a non-convex data term (MC-TV stencil in phase G and / or the ME-TV prelude B): a separate
+// instantiation, so that the plain kernel keeps its register budget (the stencil inside the unrolled epilogue cost
+// the shared instantiation 1.3 KB of spills and 19 % of its throughput, r02m)
+template <typename real, int NT, int GW, int TW, bool NC>
 __device__ __forceinline__ void myula_band_iteration(const MyulaArgs<real>& A, BandSched& sched, long long n, real* smem,
                                                      double* red, cg::grid_group& grid) {
   if (blockIdx.x == 0 && threadIdx.x == 0) *A.n_active = 0;
-  if (A.mode == 0) mband_grad_sweep0<real, NT, GW>(A, sched, smem, red);
+  if (!NC || A.mode == 0) mband_grad_sweep0<real, NT, GW, NC>(A, sched, smem, red);
   else mband_tv_sweep<real, TW>(A, sched, 0, smem, red);   // prox-only pipeline: sweep 0 without the data term
   grid.sync();
   phase_tv_scalar(A, 0);
@@ -379,12 +382,12 @@ __device__ __forceinline__ void myula_band_iteration(const MyulaArgs<real>& A, B
     phase_tv_scalar(A, it);
     grid.sync();
   }
-  mband_update<real, TW>(A, sched, n, smem);
+  mband_update<real, TW, NC>(A, sched, n, smem);
   grid.sync();
 }
 
 // A = the sampler, B = the ME-TV prelude or disabled (see img_myula_kernel)
-template <typename real, int NT, int GW, int TW>
+template <typename real, int NT, int GW, int TW, bool NC>
 __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid_constant__ MyulaArgs<real> A,
                                                                     const __grid_constant__ MyulaArgs<real> B) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -399,8 +402,8 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid
     smem[idx] = real(0);
   grid.sync();
   for (long long n = 0; n < A.N; ++n) {
-    if (B.mode == 2) myula_band_iteration<real, NT, GW, TW>(B, sched, n, smem, red, grid);
-    myula_band_iteration<real, NT, GW, TW>(A, sched, n, smem, red, grid);
+    if (NC && B.mode == 2) myula_band_iteration<real, NT, GW, TW, true>(B, sched, n, smem, red, grid);
+    myula_band_iteration<real, NT, GW, TW, NC>(A, sched, n, smem, red, grid);
   }
 }
 

@@ -175,7 +175,13 @@ class MixtureSampler:
         lib = _lib.load()
         dev = theta.device
         ws_bytes = lib.lmc_mix_workspace_bytes(Cn)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        # one workspace per (device, stream), grown on demand and reused by later launches: launches on one stream are
+        # ordered, so the next launch may overwrite it (statistics are reduced into the caller's buffers by then)
+        key = (dev, torch.cuda.current_stream(dev).cuda_stream)
+        cache = self.__dict__.setdefault("_ws_cache", {})
+        ws = cache.get(key)
+        if ws is None or ws.numel() < ws_bytes:
+            ws = cache[key] = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         io = _lib.MixIo()
         io.d_theta = theta.data_ptr()
         io.d_noise = noise.data_ptr() if noise is not None else None
