@@ -319,6 +319,18 @@ int lmc_img_sample_metrics(const lmc_img_problem* pb, int dtype, int isotropic, 
                            const void* d_x, const void* d_xtrue, double* d_out, void* d_workspace,
                            size_t workspace_bytes, void* stream);
 
+/* lmc_img_sample_metrics without a workspace argument and without any allocation (no cudaMalloc / cudaFree or
+ * allocating library call): the partial sums live in a static device array inside the library, 512 KiB per GPU, held
+ * until exit.  NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * allocate (CUDA graph capture, serving loops).  Same arguments, kernels and results (bit for bit) as
+ * lmc_img_sample_metrics; M > LMC_METRICS_STATIC_MAX_IMAGES is rejected (-1, lmc_last_error()).  All calls on a
+ * device share the one array: calls that overlap on the GPU (different streams, no dependency between them) race --
+ * serialise them.  Nothing has to be cleared between calls (every partial is written before it is read). */
+#define LMC_METRICS_STATIC_MAX_IMAGES 1024
+int lmc_img_sample_metrics_static(const lmc_img_problem* pb, int dtype, int isotropic, int64_t M,
+                                  int64_t images_per_chain, const void* d_x, const void* d_xtrue, double* d_out,
+                                  void* stream);
+
 /* 2-Wasserstein distance between two uniformly weighted point sets on the device -- the evaluation the
  * reference's mixture drivers run on the CPU with POT, ot.emd2(a, b, ot.dist(Z1, Z[:k+1]))**.5
  * (lmc.py:386-416, lmc_laplace.py:426-451).  d_x (n,dim), d_y (m,dim) row-major fp64, dim <= 4.  Log-domain

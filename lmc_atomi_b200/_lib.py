@@ -149,6 +149,8 @@ SIGNATURES = {
     "lmc_img_metrics_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "lmc_img_sample_metrics": (C.c_int, [C.POINTER(ImgProblem), C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lmc_img_sample_metrics_static": (C.c_int, [C.POINTER(ImgProblem), C.c_int, C.c_int, C.c_int64, C.c_int64,
+                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lmc_img_pd_arg": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_double, C.c_int64, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p]),
     "lmc_w2_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),

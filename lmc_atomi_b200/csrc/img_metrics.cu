@@ -4,6 +4,8 @@
 //   [0] ||H x - b||^2   [1] sum_pixels |G x|  (isotropic: l2 norm of the two differences; else l1)
 //   [2] ||x - x*||^2    [3] ||x*||^2
 // One work item = (image, slice of its tiles); fp64 accumulation, fixed-order reductions: deterministic.
+#include <mutex>
+
 #include "img_common.cuh"
 
 using namespace lmcimg;
@@ -117,4 +119,54 @@ extern "C" int lmc_img_sample_metrics(const lmc_img_problem* pb, int dtype, int 
   return dtype == LMC_F64
              ? run_metrics<double>(pb, isotropic, M, images_per_chain, d_x, d_xtrue, d_out, d_workspace, st)
              : run_metrics<float>(pb, isotropic, M, images_per_chain, d_x, d_xtrue, d_out, d_workspace, st);
+}
+
+// ------------------------------------------------------------------ no-allocation variant
+// Same kernels, same arguments and results as lmc_img_sample_metrics, but the per-slice partial sums live in a
+// file-scope device array instead of a caller-supplied workspace: for callers that cannot allocate (CUDA graph
+// capture, serving loops).  Every GPU that loads the library holds LMC_METRICS_STATIC_MAX_IMAGES * 16 * 4 doubles
+// (512 KiB) until exit.  `metrics_scratch` is a host-side stand-in here, NOT a device address: the device address
+// is looked up once per device with cudaGetSymbolAddress, with that device current, and cached.
+// Every (image, slice, quantity) partial is written by img_metrics_kernel before img_metrics_reduce_kernel reads it
+// in the same call, so nothing of the previous call's contents has to be cleared.  All calls on a device share the
+// array: two calls that overlap on the GPU (different streams, no dependency) race.
+static __device__ __align__(256) double metrics_scratch[(size_t)LMC_METRICS_STATIC_MAX_IMAGES * MET_SLICES * MET_NQ];
+
+namespace {
+constexpr int MET_MAX_DEVICES = 64;
+std::mutex metrics_scratch_mu;
+double* metrics_scratch_ptr[MET_MAX_DEVICES] = {};
+}  // namespace
+
+extern "C" int lmc_img_sample_metrics_static(const lmc_img_problem* pb, int dtype, int isotropic, int64_t M,
+                                             int64_t images_per_chain, const void* d_x, const void* d_xtrue,
+                                             double* d_out, void* stream) {
+  if (check_problem(pb, "lmc_img_sample_metrics_static") != 0) return -1;
+  LMC_REQUIRE(dtype == LMC_F32 || dtype == LMC_F64, "lmc_img_sample_metrics_static: bad dtype");
+  if (M <= 0) return 0;
+  LMC_REQUIRE(M <= LMC_METRICS_STATIC_MAX_IMAGES,
+              "lmc_img_sample_metrics_static: M = %lld images exceeds the static scratch (max %d); split the call or "
+              "use lmc_img_sample_metrics with a workspace", (long long)M, LMC_METRICS_STATIC_MAX_IMAGES);
+  LMC_REQUIRE(images_per_chain >= 1, "lmc_img_sample_metrics_static: images_per_chain must be >= 1");
+  LMC_REQUIRE(d_x && d_out && pb->d_b, "lmc_img_sample_metrics_static: d_x, d_out and pb->d_b are required");
+  LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
+              "lmc_img_sample_metrics_static: b_chain_stride must be 0 or ny*nx");
+  int dev = -1;
+  LMC_CUDA_OK(cudaGetDevice(&dev));
+  LMC_REQUIRE(dev >= 0 && dev < MET_MAX_DEVICES, "lmc_img_sample_metrics_static: device ordinal %d out of range", dev);
+  double* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(metrics_scratch_mu);
+    if (metrics_scratch_ptr[dev] == nullptr) {   // once per device, with that device current
+      void* p = nullptr;
+      LMC_CUDA_OK(cudaGetSymbolAddress(&p, metrics_scratch));
+      LMC_REQUIRE(p != nullptr, "lmc_img_sample_metrics_static: cudaGetSymbolAddress returned a null address");
+      metrics_scratch_ptr[dev] = (double*)p;
+    }
+    scratch = metrics_scratch_ptr[dev];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  return dtype == LMC_F64
+             ? run_metrics<double>(pb, isotropic, M, images_per_chain, d_x, d_xtrue, d_out, scratch, st)
+             : run_metrics<float>(pb, isotropic, M, images_per_chain, d_x, d_xtrue, d_out, scratch, st);
 }
