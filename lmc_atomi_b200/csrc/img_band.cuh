@@ -63,13 +63,106 @@ __device__ __forceinline__ void band_block_sum2(double& a, double& b, double* re
   }
 }
 
-// rows [ifirst, ifirst + rows) of src -> S (zero outside the image), as 16-byte cp.async copies when the
-// rows are 16-byte aligned.  Ends with the data visible to the whole CTA.
+// Dynamic work distribution: the CTAs of a phase draw items from a global counter instead of striding, so
+// a CTA on a slower path to memory (far L2 partition, busier SM) simply takes fewer items and the grid
+// barrier at the end of the phase is reached together.  Thread 0 draws the next item at the START of the
+// current one (the atomic's latency is covered by the item) and publishes it through shared memory at the
+// barrier that opens the next round.  Results do not depend on which CTA ran an item (one partial per item).
+struct BandSched {
+  int* q;        // 4 rotating global counters: phase p uses q[p & 3] and re-arms q[(p + 2) & 3]
+  int* s_next;   // 2 shared ints (double-buffered by round)
+  int phase, round, nxt;
+  unsigned tma_par;   // phase parity of the staging mbarrier (band_stage), tracked per thread
+  __device__ __forceinline__ void begin() {
+    if (blockIdx.x == 0 && threadIdx.x == 0) q[(phase + 2) & 3] = gridDim.x;
+    nxt = blockIdx.x;
+  }
+  __device__ __forceinline__ int next(int items) {   // also the barrier that frees the staging buffers
+    int* slot = s_next + (round & 1);
+    if (threadIdx.x == 0) *slot = nxt;
+    __syncthreads();
+    ++round;
+    const int w = *slot;
+    if (w < items && threadIdx.x == 0) nxt = atomicAdd(q + (phase & 3), 1);
+    return w;
+  }
+  __device__ __forceinline__ void end() { ++phase; }
+};
+
+
+// ---------------------------------------------------------------- staging through the TMA engine
+// band_stage moves whole image rows: with 16-byte aligned rows each is ONE 1-D bulk copy (cp.async.bulk global ->
+// shared, SASS UBLKCP) issued by a lane of warp 0 and tracked by an mbarrier (expect_tx = bytes of the in-image rows);
+// the other warps issue nothing and go straight to the wait.  Rows outside the image are zero-filled by the CTA.
+#ifndef LMC_BAND_TMA
+#define LMC_BAND_TMA 1
+#endif
+__device__ __forceinline__ unsigned long long& band_mbar() {
+  __shared__ __align__(8) unsigned long long bar;
+  return bar;
+}
+__device__ __forceinline__ void band_tma_init(BandSched& sched) {
+  sched.tma_par = 0;
+  if (threadIdx.x == 0) {
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(&band_mbar());
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+}
+
+// rows [ifirst, ifirst + rows) of src -> S (zero outside the image): bulk copies (above) when the rows are 16-byte
+// aligned, else element copies.  Ends with the data visible to the whole CTA.  The caller's preceding barrier
+// (BandSched::next or __syncthreads) has retired every access to S of the previous item.
 template <typename real>
-__device__ __forceinline__ void band_stage(real* S, int pitch, const real* __restrict__ src, int ny, int nx, int ifirst,
-                                           int rows) {
+__device__ __forceinline__ void band_stage(BandSched& sched, real* S, int pitch, const real* __restrict__ src, int ny,
+                                           int nx, int ifirst, int rows) {
   constexpr int EPV = 16 / sizeof(real);
   const bool vec = (nx % EPV == 0) && ((reinterpret_cast<size_t>(src) & 15) == 0);
+#if LMC_BAND_TMA
+  if (vec && rows <= 32) {
+    const int a = ifirst > 0 ? ifirst : 0, b = (ifirst + rows < ny) ? ifirst + rows : ny;   // in-image rows [a, b)
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(&band_mbar());
+    const unsigned row_bytes = (unsigned)nx * (unsigned)sizeof(real);
+    if (threadIdx.x < 32) {
+      if (threadIdx.x == 0) {
+        // generic-proxy writes to S (zero fill, previous phases) are ordered before the async-proxy writes below
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+                     "r"((unsigned)(b > a ? b - a : 0) * row_bytes)
+                     : "memory");
+      }
+      __syncwarp();
+      const int r = (int)threadIdx.x, i = ifirst + r;
+      if (r < rows && i >= a && i < b) {
+        const unsigned d = (unsigned)__cvta_generic_to_shared(S + r * pitch + BAND_PAD);
+        const real* s = src + (long long)i * nx;
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(d),
+                     "l"(s), "r"(row_bytes), "r"(bar)
+                     : "memory");
+      }
+    }
+    if (a > ifirst || b < ifirst + rows) {   // top / bottom bands only (uniform over the CTA)
+      for (int r = 0; r < rows; ++r) {
+        const int i = ifirst + r;
+        if (i >= 0 && i < ny) continue;
+        for (int c = threadIdx.x * EPV; c < nx; c += BAND_BT * EPV)
+          *reinterpret_cast<uint4*>(S + r * pitch + BAND_PAD + c) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      __syncthreads();
+    }
+    unsigned done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(bar), "r"(sched.tma_par)
+          : "memory");
+    }
+    sched.tma_par ^= 1u;
+    return;
+  }
+#endif
   const int cpr = nx / EPV;   // 16-byte chunks per row
   if (vec && cpr <= BAND_BT && BAND_BT % cpr == 0) {
     // a thread keeps its chunk column and walks down the rows: no per-copy index arithmetic
@@ -255,29 +348,23 @@ __device__ __forceinline__ void band_of(const Geom<real>& g, int w, long long c_
   i0 = (w - cl * g.tiles) * RB;
 }
 
-// Dynamic work distribution: the CTAs of a phase draw items from a global counter instead of striding, so
-// a CTA on a slower path to memory (far L2 partition, busier SM) simply takes fewer items and the grid
-// barrier at the end of the phase is reached together.  Thread 0 draws the next item at the START of the
-// current one (the atomic's latency is covered by the item) and publishes it through shared memory at the
-// barrier that opens the next round.  Results do not depend on which CTA ran an item (one partial per item).
-struct BandSched {
-  int* q;        // 4 rotating global counters: phase p uses q[p & 3] and re-arms q[(p + 2) & 3]
-  int* s_next;   // 2 shared ints (double-buffered by round)
-  int phase, round, nxt;
-  __device__ __forceinline__ void begin() {
-    if (blockIdx.x == 0 && threadIdx.x == 0) q[(phase + 2) & 3] = gridDim.x;
-    nxt = blockIdx.x;
-  }
-  __device__ __forceinline__ int next(int items) {   // also the barrier that frees the staging buffers
-    int* slot = s_next + (round & 1);
-    if (threadIdx.x == 0) *slot = nxt;
-    __syncthreads();
-    ++round;
-    const int w = *slot;
-    if (w < items && threadIdx.x == 0) nxt = atomicAdd(q + (phase & 3), 1);
-    return w;
-  }
-  __device__ __forceinline__ void end() { ++phase; }
-};
+// L2 prefetch of rows [r0, r0 + rows) of one image (clamped to the image): one bulk-prefetch instruction
+// (cp.async.bulk.prefetch.L2, SASS UBLKPF) issued by a single thread for the rows the CTA's NEXT work item will stage,
+// so that its staging loads find them in L2 instead of paying the HBM latency in front of the forward pass.
+#ifndef LMC_BAND_L2_PREFETCH
+#define LMC_BAND_L2_PREFETCH 1
+#endif
+template <typename real>
+__device__ __forceinline__ void band_l2_prefetch(const real* base, int ny, int nx, int r0, int rows) {
+#if LMC_BAND_L2_PREFETCH
+  const int a = r0 > 0 ? r0 : 0, b = (r0 + rows < ny) ? r0 + rows : ny;
+  if (b <= a) return;
+  size_t p0 = (size_t)(base + (size_t)a * nx), p1 = (size_t)(base + (size_t)b * nx);
+  p0 = (p0 + 15) & ~(size_t)15;
+  p1 &= ~(size_t)15;
+  if (p1 > p0)
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p0), "r"((unsigned)(p1 - p0)) : "memory");
+#endif
+}
 
 }  // namespace lmcimg

@@ -131,7 +131,7 @@ __device__ void mband_grad_sweep0(const MyulaArgs<real>& A, BandSched& sched, re
     real* gout = A.grad + chain * g.P;
     real* p1 = dual_ptr(A, 1, 0, chain);
     real* q1 = dual_ptr(A, 1, 1, chain);
-    band_stage(X, pitch, A.x + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
+    band_stage(sched, X, pitch, A.x + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, GW>(g, X, T, pitch, i0, wx, wy,
                                      [&](int i, int c) { return ldp<real, GW>(bc + i * g.nx + c); });
     __syncthreads();
@@ -400,6 +400,7 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_myula_band_kernel(const __grid
   // pad columns (and everything else) zero once; the phases only ever write columns [0, nx)
   for (int idx = threadIdx.x; idx < (int)(myula_band_smem_bytes<real, NT>(A.pitch) / sizeof(real)); idx += BAND_BT)
     smem[idx] = real(0);
+  band_tma_init(sched);
   grid.sync();
   for (long long n = 0; n < A.N; ++n) {
     if (NC && B.mode == 2) myula_band_iteration<real, NT, GW, TW, true>(B, sched, n, smem, red, grid);

@@ -28,7 +28,7 @@ namespace {
 
 // ---------------------------------------------------------------- P0: optb = sigma H^T b
 template <typename real, int NT, int RB, int W>
-__device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real* wx, const real* wy) {
+__device__ void band_optb(const UlpdaArgs<real>& A, BandSched& sched, real* smem, const real* wx, const real* wy) {
   const long long c_lo = 0, c_hi = A.b_stride ? A.C : 1;
   const int hi_y = A.g.lo_y + NT - 1;
   const Geom<real>& g = A.g;
@@ -39,7 +39,7 @@ __device__ void band_optb(const UlpdaArgs<real>& A, real* smem, const real* wx, 
     long long chain; int i0;
     band_of(g, w, c_lo, RB, chain, i0);
     __syncthreads();
-    band_stage(T, pitch, A.b + chain * A.b_stride, g.ny, g.nx, i0 - hi_y, Band<real, NT, RB>::TROWS);
+    band_stage(sched, T, pitch, A.b + chain * A.b_stride, g.ny, g.nx, i0 - hi_y, Band<real, NT, RB>::TROWS);
     real* ob = A.optb + chain * g.P;
     BandPf<real, W, 0, 4> pf;
     band_adjoint<real, NT, RB, W, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, Pack<real, W> (&)[1]) {},
@@ -95,7 +95,7 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, BandSched& sched, lon
     band_prefetch<real, RB, W, 2, 4>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
     if (A.warm_on) {
-      band_stage(X, pitch, zw, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
+      band_stage(sched, X, pitch, zw, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     } else {
       for (int r = 0; r < Band<real, NT, RB>::XROWS; ++r)
         for (int c = threadIdx.x; c < g.nx; c += BAND_BT) X[r * pitch + BAND_PAD + c] = real(0);
@@ -145,7 +145,7 @@ __device__ void band_v0(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     real* vC = A.v + chain * g.P;
     real* wC = A.w + chain * g.P;
     __syncthreads();
-    band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
+    band_stage(sched, X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
     double acc = 0, none = 0;
@@ -196,9 +196,24 @@ __device__ void band_ka(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     BandPf<real, W, 3, 4> pf;
     band_prefetch<real, RB, W, 3, 4>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
-    band_stage(X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
+    band_stage(sched, X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
+#if LMC_BAND_L2_PREFETCH
+    if (threadIdx.x == 0 && sched.nxt < items) {   // the next item's staged rows and epilogue operands -> L2
+      long long cn; int in;
+      band_of(g, sched.nxt, c_lo, RB, cn, in);
+      const LsqrState* sn = A.st + cn;
+      if (sn->active) {
+        band_l2_prefetch(A.v + cn * g.P, g.ny, g.nx, in - E, Band<real, NT, RB>::XROWS);
+        band_l2_prefetch(A.u + cn * g.P, g.ny, g.nx, in, RB);
+        if (sn->pending) {
+          band_l2_prefetch(A.w + cn * g.P, g.ny, g.nx, in, RB);
+          band_l2_prefetch(A.warm + cn * g.P, g.ny, g.nx, in, RB);
+        }
+      }
+    }
+#endif
     double accu = 0, accw = 0;
     band_adjoint<real, NT, RB, W, 3, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
                                                                               const Pack<real, W> (&v)[3]) {
@@ -249,9 +264,20 @@ __device__ void band_kb(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     BandPf<real, W, 1, 4> pf;
     band_prefetch<real, RB, W, 1, 4>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
-    band_stage(X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
+    band_stage(sched, X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
+#if LMC_BAND_L2_PREFETCH
+    if (threadIdx.x == 0 && sched.nxt < items) {
+      long long cn; int in;
+      band_of(g, sched.nxt, c_lo, RB, cn, in);
+      const LsqrState* sn = A.st + cn;
+      if (sn->active && sn->beta > 0) {
+        band_l2_prefetch(A.u + cn * g.P, g.ny, g.nx, in - E, Band<real, NT, RB>::XROWS);
+        band_l2_prefetch(A.v + cn * g.P, g.ny, g.nx, in, RB);
+      }
+    }
+#endif
     double acc = 0, none = 0;
     band_adjoint<real, NT, RB, W, 1, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
                                                                               const Pack<real, W> (&v)[1]) {
@@ -445,7 +471,8 @@ __global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid
     for (int idx = threadIdx.x; idx < n; idx += BAND_BT) smem[idx] = real(0);
   }
   __syncthreads();
-  band_optb<real, NT, RB, W>(A, smem, wx, wy);
+  band_tma_init(sched);
+  band_optb<real, NT, RB, W>(A, sched, smem, wx, wy);
   grid.sync();
   for (long long c_lo = 0; c_lo < A.C; c_lo += A.group) {
     const long long c_hi = (c_lo + A.group < A.C) ? c_lo + A.group : A.C;

@@ -26,14 +26,15 @@ for (loc, txt), r in zip(seq, body):
     for i in stall_cols:
         v = int(r[i] or 0)
         if v: st[loc][hdr[i][6:]] += v
-src = open(srcf).read().split('\n')
-base = srcf.split('/')[-1]
+import os
+srcdir = os.path.dirname(srcf)
+srcs = {f: open(os.path.join(srcdir, f)).read().split('\n') for f in os.listdir(srcdir) if f.endswith(('.cu', '.cuh', '.inl'))}
 tots = collections.Counter()
 for loc in st:
     for k, v in st[loc].items(): tots[k] += v
 print('stall totals:', ', '.join(f'{k} {v/totS*100:.1f}%' for k, v in tots.most_common(10)))
 for key, c in sorted(aggS.items(), key=lambda kv: -kv[1])[:int(sys.argv[5]) if len(sys.argv) > 5 else 40]:
     f, l = key if key else ('?', 0)
-    s = src[l - 1].strip()[:70] if f == base else f
+    s = srcs[f][l - 1].strip()[:90] if f in srcs and 0 < l <= len(srcs[f]) else f
     top = ', '.join(f'{k}:{v/totS*100:.1f}' for k, v in st[key].most_common(3))
     print(f'{f[:12]:12s}:{l:4d} inst {agg[key]/tot*100:5.2f}% smp {c/totS*100:5.2f}% [{top}]  {s}')
