@@ -3,7 +3,10 @@
 
 namespace {
 
-constexpr int BAND_RB = 16;   // rows per band
+#ifndef LMC_ULPDA_BAND_RB
+#define LMC_ULPDA_BAND_RB 16
+#endif
+constexpr int BAND_RB = LMC_ULPDA_BAND_RB;   // rows per band
 
 template <typename real>
 size_t ulpda_ws_bytes(int ny, int nx, long long C) {
@@ -186,11 +189,16 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
   }
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
   if (band) {
+#ifdef LMC_IMG_BENCH_ONLY   // experiment builds (scripts/): the H5 pair kernel only
+    if constexpr (sizeof(real) == 4) return launch_band<real, 5, 2>(A, B, st);
+    else return -1;
+#else
     switch (pb->ntap_y) {
       case 5: return band_pairs(A) ? launch_band<real, 5, 2>(A, B, st) : launch_band<real, 5, 1>(A, B, st);
       case 6: return band_pairs(A) ? launch_band<real, 6, 2>(A, B, st) : launch_band<real, 6, 1>(A, B, st);
       default: return band_pairs(A) ? launch_band<real, 7, 2>(A, B, st) : launch_band<real, 7, 1>(A, B, st);
     }
+#endif
   }
   {   // the second kernel argument has its own type: launch by hand
     int dev = 0, sms = 0, occ = 0;

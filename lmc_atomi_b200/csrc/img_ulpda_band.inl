@@ -15,6 +15,15 @@
 
 namespace {
 
+// rows per block of register-prefetched epilogue operands (two blocks in flight).  Measured at 512 x 512 x 512 chains
+// (r02u / r02v): depth 4 -> 33.0 k chain-iters/s with 1.4 KB of spills at the 128-register cap, 2 -> 35.0 k, 1 -> 35.9 k
+// (132 B of spills): the next item's rows are already on their way to L2 (band_l2_prefetch), so two rows of distance
+// cover what is left of the latency and the registers are worth more to the unrolled filter passes.
+#ifndef LMC_ULPDA_PFD
+#define LMC_ULPDA_PFD 1
+#endif
+constexpr int UB_PFD = LMC_ULPDA_PFD;
+
 #define BAND_ITEMS_LOOP                                                        \
   const Geom<real>& g = A.g;                                                   \
   real* X = smem;                                                              \
@@ -41,8 +50,8 @@ __device__ void band_optb(const UlpdaArgs<real>& A, BandSched& sched, real* smem
     __syncthreads();
     band_stage(sched, T, pitch, A.b + chain * A.b_stride, g.ny, g.nx, i0 - hi_y, Band<real, NT, RB>::TROWS);
     real* ob = A.optb + chain * g.P;
-    BandPf<real, W, 0, 4> pf;
-    band_adjoint<real, NT, RB, W, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, Pack<real, W> (&)[1]) {},
+    BandPf<real, W, 0, UB_PFD> pf;
+    band_adjoint<real, NT, RB, W, 0, UB_PFD>(g, T, pitch, i0, wx, wy, pf, [&](int, int, Pack<real, W> (&)[1]) {},
                                         [&](int i, int c, int, const Pack<real, W>& gv, const Pack<real, W> (&)[1]) {
                                           Pack<real, W> o;
 #pragma unroll
@@ -91,8 +100,8 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, BandSched& sched, lon
       }
       v[1] = ldp<real, W>(ob + o);
     };
-    BandPf<real, W, 2, 4> pf;
-    band_prefetch<real, RB, W, 2, 4>(g, i0, W * threadIdx.x, pf, pre);
+    BandPf<real, W, 2, UB_PFD> pf;
+    band_prefetch<real, RB, W, 2, UB_PFD>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
     if (A.warm_on) {
       band_stage(sched, X, pitch, zw, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
@@ -104,7 +113,7 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, BandSched& sched, lon
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
     double accb = 0, accu = 0;
-    band_adjoint<real, NT, RB, W, 2, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
+    band_adjoint<real, NT, RB, W, 2, UB_PFD>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
                                                                               const Pack<real, W> (&v)[2]) {
       const int o = i * g.nx + c;
       const Pack<real, W> zc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
@@ -149,8 +158,8 @@ __device__ void band_v0(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
     double acc = 0, none = 0;
-    BandPf<real, W, 0, 4> pf;
-    band_adjoint<real, NT, RB, W, 0, 4>(g, T, pitch, i0, wx, wy, pf, [&](int, int, Pack<real, W> (&)[1]) {},
+    BandPf<real, W, 0, UB_PFD> pf;
+    band_adjoint<real, NT, RB, W, 0, UB_PFD>(g, T, pitch, i0, wx, wy, pf, [&](int, int, Pack<real, W> (&)[1]) {},
                                         [&](int i, int c, int k, const Pack<real, W>& gv, const Pack<real, W> (&)[1]) {
       const int o = i * g.nx + c;
       const Pack<real, W> xc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
@@ -193,8 +202,8 @@ __device__ void band_ka(const UlpdaArgs<real>& A, BandSched& sched, long long c_
         v[2] = ldp<real, W>(zC + o);
       }
     };
-    BandPf<real, W, 3, 4> pf;
-    band_prefetch<real, RB, W, 3, 4>(g, i0, W * threadIdx.x, pf, pre);
+    BandPf<real, W, 3, UB_PFD> pf;
+    band_prefetch<real, RB, W, 3, UB_PFD>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
     band_stage(sched, X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
@@ -215,7 +224,7 @@ __device__ void band_ka(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     }
 #endif
     double accu = 0, accw = 0;
-    band_adjoint<real, NT, RB, W, 3, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
+    band_adjoint<real, NT, RB, W, 3, UB_PFD>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
                                                                               const Pack<real, W> (&v)[3]) {
       const int o = i * g.nx + c;
       const Pack<real, W> xc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
@@ -261,8 +270,8 @@ __device__ void band_kb(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     const real su = (real)sp->su, sv = (real)sp->sv, beta = (real)sp->beta;
     real* vC = A.v + chain * g.P;
     auto pre = [&](int i, int c, Pack<real, W> (&v)[1]) { v[0] = ldp<real, W>(vC + i * g.nx + c); };
-    BandPf<real, W, 1, 4> pf;
-    band_prefetch<real, RB, W, 1, 4>(g, i0, W * threadIdx.x, pf, pre);
+    BandPf<real, W, 1, UB_PFD> pf;
+    band_prefetch<real, RB, W, 1, UB_PFD>(g, i0, W * threadIdx.x, pf, pre);
     __syncthreads();
     band_stage(sched, X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
@@ -279,7 +288,7 @@ __device__ void band_kb(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     }
 #endif
     double acc = 0, none = 0;
-    band_adjoint<real, NT, RB, W, 1, 4>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
+    band_adjoint<real, NT, RB, W, 1, UB_PFD>(g, T, pitch, i0, wx, wy, pf, pre, [&](int i, int c, int k, const Pack<real, W>& gv,
                                                                               const Pack<real, W> (&v)[1]) {
       const int o = i * g.nx + c;
       const Pack<real, W> xc = ldp<real, W>(X + (k + E) * pitch + BAND_PAD + c);
@@ -452,8 +461,11 @@ __device__ void band_dual(const UlpdaArgs<real>& A, BandSched& sched, long long 
   }
 }
 
+#ifndef LMC_ULPDA_BAND_MINB
+#define LMC_ULPDA_BAND_MINB 2
+#endif
 template <typename real, int NT, int RB, int W>
-__global__ void __launch_bounds__(BAND_BT, 2) img_ulpda_band_kernel(const __grid_constant__ UlpdaArgs<real> A,
+__global__ void __launch_bounds__(BAND_BT, LMC_ULPDA_BAND_MINB) img_ulpda_band_kernel(const __grid_constant__ UlpdaArgs<real> A,
                                                                     const __grid_constant__ MyulaArgs<real> B) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   real* smem = reinterpret_cast<real*>(smem_raw);

@@ -129,12 +129,12 @@ def ulpda_band_min_bytes_per_pixel(k_exec: float, itemsize: int = 4) -> float:
 
 # ---- measured with `ncu --set full` (files under profiles/): dram__bytes_read.sum + dram__bytes_write.sum per launch
 # divided by the chain-iterations of that launch, and executed thread-instructions per pixel-iteration.
-ULPDA_BAND = {"profile": "profiles/r01g_img_ulpda_band_ncu_full_summary.csv",
-              "dram_bytes_per_chain_iter": (34.459e9 + 23.259e9) / 512.0,      # 512x512, H5, k = 8
-              "issue_active_pct": 38.7}
-MYULA_BAND = {"profile": "profiles/r01g_img_myula_band_ncu_full_summary.csv",
-              "dram_bytes_per_chain_iter": (74.037e9 + 36.859e9) / 2560.0,     # 512x512, H5, fp32
-              "issue_active_pct": 41.0}
+ULPDA_BAND = {"profile": "profiles/r02r_img_ulpda_band_ncu_full_summary.csv",
+              "dram_bytes_per_chain_iter": (39.793e9 + 26.921e9) / 592.0,      # 512x512, H5, 296 chains x 2, k = 8.7
+              "issue_active_pct": 39.0}
+MYULA_BAND = {"profile": "profiles/r02r_img_myula_band_ncu_full_summary.csv",
+              "dram_bytes_per_chain_iter": (57.926e9 + 28.210e9) / 1776.0,     # 512x512, H5, fp32, 296 chains x 6
+              "issue_active_pct": 41.7}
 MYULA_ONCHIP = {"profile": "profiles/r01c_img_myula_onchip_ncu_full_summary.csv",
                 "dram_bytes_per_chain_iter": (134.6e6 + 86.6e6) / 2560.0,      # 256x256: b prefetch + mean
                 "thread_instr_per_pixel_iter": 395.0, "issue_active_pct": 54.7, "sms_used": 120}
