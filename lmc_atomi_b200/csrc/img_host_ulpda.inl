@@ -1,12 +1,19 @@
 // Host side of img_ulpda.cu: workspace layout, argument marshalling, C entry points.
 #include "img_host_common.inl"
 
+// The band kernels are instantiated per tap count in their own translation units (img_ulpda_band{5,6,7}.cu, compiled
+// in parallel): dtype and w (image columns per thread) are resolved there.  A / B are UlpdaArgs / MyulaArgs<float|double>.
+int lmc_ulpda_band_launch_nt5(int dtype, void* A, const void* B, int w, cudaStream_t st);
+int lmc_ulpda_band_launch_nt6(int dtype, void* A, const void* B, int w, cudaStream_t st);
+int lmc_ulpda_band_launch_nt7(int dtype, void* A, const void* B, int w, cudaStream_t st);
+
 namespace {
 
+// rows per band of the band kernel (img_ulpda_band.inl)
 #ifndef LMC_ULPDA_BAND_RB
 #define LMC_ULPDA_BAND_RB 16
 #endif
-constexpr int BAND_RB = LMC_ULPDA_BAND_RB;   // rows per band
+constexpr int BAND_RB = LMC_ULPDA_BAND_RB;
 
 template <typename real>
 size_t ulpda_ws_bytes(int ny, int nx, long long C) {
@@ -49,28 +56,6 @@ bool band_pairs(const UlpdaArgs<real>& A) {
   for (const void* p : ptrs)
     if (reinterpret_cast<size_t>(p) % (2 * sizeof(real)) != 0) return false;
   return true;
-}
-
-template <typename real, int NT, int W>
-int launch_band(UlpdaArgs<real>& A, const MyulaArgs<real>& B, cudaStream_t st) {
-  size_t smem = Band<real, NT, BAND_RB>::smem_bytes(A.pitch);
-  if (B.mode == 3 && smem < (size_t)4 * RS * RS * sizeof(real)) smem = (size_t)4 * RS * RS * sizeof(real);   // tile TV phases
-  auto kern = img_ulpda_band_kernel<real, NT, BAND_RB, W>;
-  int dev = 0, sms = 0, occ = 0;
-  LMC_CUDA_OK(cudaGetDevice(&dev));
-  LMC_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  LMC_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  LMC_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, BAND_BT, smem));
-  LMC_REQUIRE(occ >= 1, "ULPDA band kernel does not fit on an SM (smem %zu)", smem);
-  const long long cap = (long long)sms * occ;
-  const long long g = A.group < A.C ? A.group : A.C;
-  const long long items = g * A.g.tiles;
-  LMC_REQUIRE(items < (1ll << 31) && A.g.P < (1ll << 31), "ULPDA band kernel: 32-bit item / pixel indices exceeded");
-  int grid = (int)(items < cap ? items : cap);
-  if (grid < 1) grid = 1;
-  void* kargs[] = {(void*)&A, (void*)&B};
-  LMC_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(BAND_BT), kargs, smem, st));
-  return 0;
 }
 
 template <typename real>
@@ -189,16 +174,12 @@ int run_ulpda(const lmc_img_problem* pb, const lmc_img_ulpda_params* pr, long lo
   }
   LMC_CUDA_OK(cudaMemsetAsync(io->d_workspace, 0, 256, st));
   if (band) {
-#ifdef LMC_IMG_BENCH_ONLY   // experiment builds (scripts/): the H5 pair kernel only
-    if constexpr (sizeof(real) == 4) return launch_band<real, 5, 2>(A, B, st);
-    else return -1;
-#else
+    const int dt = sizeof(real) == 8 ? LMC_F64 : LMC_F32, w = band_pairs(A) ? 2 : 1;
     switch (pb->ntap_y) {
-      case 5: return band_pairs(A) ? launch_band<real, 5, 2>(A, B, st) : launch_band<real, 5, 1>(A, B, st);
-      case 6: return band_pairs(A) ? launch_band<real, 6, 2>(A, B, st) : launch_band<real, 6, 1>(A, B, st);
-      default: return band_pairs(A) ? launch_band<real, 7, 2>(A, B, st) : launch_band<real, 7, 1>(A, B, st);
+      case 5: return lmc_ulpda_band_launch_nt5(dt, &A, &B, w, st);
+      case 6: return lmc_ulpda_band_launch_nt6(dt, &A, &B, w, st);
+      default: return lmc_ulpda_band_launch_nt7(dt, &A, &B, w, st);
     }
-#endif
   }
   {   // the second kernel argument has its own type: launch by hand
     int dev = 0, sms = 0, occ = 0;

@@ -1,5 +1,5 @@
-// ULPDA, row-band formulation (included by img_ulpda.cu; same arguments, LSQR state machine and
-// scalar phases as the tile kernel above, different data movement).
+// ULPDA, row-band formulation (included by img_ulpda_band_tu.inl after img_ulpda_tile.cuh; same arguments, LSQR state
+// machine and scalar phases as the tile kernel, different data movement).
 //
 // A work item is a band of RB full image rows of one chain.  The band plus its 2(NT-1) halo rows
 // is staged once in shared memory (coalesced rows, zero pad columns = the zero boundary of
