@@ -383,13 +383,25 @@ __device__ __forceinline__ real mh_logdens2(const MixP<real>& P, real t0, real t
 // State of one chain (registers of one thread) + the per-step arithmetic shared by the
 // validation loop (host-supplied noise, trajectory written every step) and the production
 // loop (Philox noise, nothing but registers touched inside the K-loop).
-template <typename real, int TARGET, int ALG, int NC>
+// MIRROR (production MLA in fp32): the chain is carried in mirror coordinates.  theta_{k+1} = beta sinh(y_{k+1}) with
+// y_{k+1} = asinh(theta_k / beta) - gamma grad U(theta_k) + noise (lmc.py:186-187), so asinh(theta_{k+1} / beta) IS
+// y_{k+1} and sqrt(theta_{k+1}^2 + beta^2) IS beta cosh(y_{k+1}): both come out of the two exponentials the sinh
+// already costs.  Saves a square root and a logarithm per coordinate and step (4 of the ~20 MUFU operations of an
+// MLA step, the pipe that bounds it: XU 74 % active in profiles/r02i) at the price of not re-rounding y through
+// sinh/asinh every step -- a relative 1e-7 per step, the size of the fp32 arithmetic itself.  Validation mode and
+// float64 keep the reference's evaluation order.
+#ifndef LMC_MIX_MLA_MIRROR
+#define LMC_MIX_MLA_MIRROR 1
+#endif
+
+template <typename real, int TARGET, int ALG, int NC, bool MIRROR = false>
 struct Chain {
   using M = Math<real>;
   using L = Lanes<real>;
   using mask = typename L::mask;
   static constexpr bool ADJ = AlgTraits<ALG>::adjusted;
   real t0, t1;
+  real my0, my1, msq0, msq1;   // MIRROR: y = asinh(theta / beta) and sqrt(theta^2 + beta^2) of the current state
   real cc0, cc1, clog;   // MH chains: proposal centre and log2-density at the current state
   typename L::count nacc;
   real b_n, b_s0, b_s1, b_s00, b_s01, b_s11;        // fp32/fp64 partial sums of <= 32 steps
@@ -407,12 +419,37 @@ struct Chain {
       drift_centre<real, ALG>(P, t0, t1, cur, cc0, cc1);
       clog = mh_logdens2<real, ALG>(P, t0, t1, cur);
     }
+    my0 = my1 = msq0 = msq1 = real(0);
+    if (MIRROR) {
+      msq0 = M::sqrt(M::fma(t0, t0, P.b0 * P.b0));
+      msq1 = M::sqrt(M::fma(t1, t1, P.b1 * P.b1));
+      my0 = mirror_asinh(t0, msq0, P.ib0);
+      my1 = mirror_asinh(t1, msq1, P.ib1);
+    }
+  }
+
+  // MLA step in mirror coordinates (see MIRROR above); same operations as step_unadjusted otherwise
+  __device__ __forceinline__ void step_mirror(const MixP<real>& P, real x0, real x1) {
+    Eval<real> e;
+    eval_target<real, TARGET, NC, false>(P, t0, t1, e);
+    real y0 = my0 - P.gamma * e.g0, y1 = my1 - P.gamma * e.g1;
+    y0 = M::fma(P.s2g * M::rsqrt(msq0), x0, y0);
+    y1 = M::fma(P.s2g * M::rsqrt(msq1), x1, y1);
+    const real a0 = y0 * real(1.4426950408889634), a1 = y1 * real(1.4426950408889634);
+    const real E0 = M::exp2(a0), F0 = M::exp2(-a0), E1 = M::exp2(a1), F1 = M::exp2(-a1);
+    t0 = P.b0 * (real(0.5) * (E0 - F0));    // beta sinh(y), as Math<float>::sinh evaluates it
+    t1 = P.b1 * (real(0.5) * (E1 - F1));
+    msq0 = P.b0 * (real(0.5) * (E0 + F0));  // beta cosh(y) = sqrt(theta^2 + beta^2)
+    msq1 = P.b1 * (real(0.5) * (E1 + F1));
+    my0 = y0;
+    my1 = y1;
   }
 
   // one transition; returns whether a sample was emitted (always, for unadjusted samplers)
   __device__ __forceinline__ mask step(const MixP<real>& P, real x0, real x1, real u) {
     if (!ADJ) {
-      step_unadjusted<real, TARGET, ALG, NC>(P, t0, t1, x0, x1);
+      if (MIRROR) step_mirror(P, x0, x1);
+      else step_unadjusted<real, TARGET, ALG, NC>(P, t0, t1, x0, x1);
       return L::not_(L::gt(real(0), real(0)));   // all lanes emit
     }
     // lmc.py:124-130: propose, MH ratio p(new) q(old|new) / (p(old) q(new|old)),
@@ -487,8 +524,8 @@ __device__ __forceinline__ void hist_lanes(const MixIo& io, real t0, real t1, ty
 // moments (steps past the burn-in), HIST = bin every io.hist_every-th emitted step.
 // Unadjusted samplers use one Philox block per TWO steps (words x,y for even k, z,w for odd
 // k, block counter k >> 1); adjusted samplers one block per step (x,y normals, z uniform).
-template <typename real, int TARGET, int ALG, int NC, bool STATS, bool HIST>
-__device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC>& ch, const MixP<real>& P,
+template <typename real, int TARGET, int ALG, int NC, bool STATS, bool HIST, bool MIRROR>
+__device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC, MIRROR>& ch, const MixP<real>& P,
                                                const MixIo& io, typename Lanes<real>::cid cid,
                                                typename Lanes<real>::mask live, long long kb, long long ke) {
   using M = Math<real>;
@@ -608,15 +645,16 @@ __global__ void __launch_bounds__(BLOCK, (Lanes<real>::N == 2 ? LMC_MIX_MINBLOCK
       auto r = L::philox(0u, LMC_STREAM_INIT, cid, io.rk);
       M::normals(r.x, r.y, a0, a1);
     }
-    Chain<real, TARGET, ALG, NC> ch;
+    constexpr bool MIRROR = LMC_MIX_MLA_MIRROR && PROD && ALG == LMC_MLA && !M::is_double;
+    Chain<real, TARGET, ALG, NC, MIRROR> ch;
     ch.init(P, a0, a1);
 
     if constexpr (PROD) {
       const long long kb = io.burnin < K ? (io.burnin > 0 ? io.burnin : 0) : K;
       const bool hist = io.hist != nullptr && io.hist_every > 0;
-      run_production<real, TARGET, ALG, NC, false, false>(ch, P, io, cid, live, 0, kb);
-      if (hist) run_production<real, TARGET, ALG, NC, true, true>(ch, P, io, cid, live, kb, K);
-      else run_production<real, TARGET, ALG, NC, true, false>(ch, P, io, cid, live, kb, K);
+      run_production<real, TARGET, ALG, NC, false, false, MIRROR>(ch, P, io, cid, live, 0, kb);
+      if (hist) run_production<real, TARGET, ALG, NC, true, true, MIRROR>(ch, P, io, cid, live, kb, K);
+      else run_production<real, TARGET, ALG, NC, true, false, MIRROR>(ch, P, io, cid, live, kb, K);
     } else {
       // validation mode (one chain per thread): the reference's own draws come from HBM, every state goes back
       static_assert(PROD || L::N == 1, "validation mode runs one chain per thread");
