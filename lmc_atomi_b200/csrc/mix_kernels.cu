@@ -48,7 +48,7 @@ struct MixP {
   // l1 prior (GAUSS_L1)
   real pr_alpha, pr_thr, pr_mu0, pr_mu1;
   // step
-  real gamma, s2g, inv4g;
+  real gamma, s2g, inv4g, inv4g_l2e;   // inv4g_l2e = log2(e) / (4 gamma)
   real m00, m01, m10, m11;      // M
   real s00, s01, s10, s11;      // sqrtm(M)
   real q00, q01, q10, q11;      // Q
@@ -462,10 +462,11 @@ struct Chain {
     real plog = mh_logdens2<real, ALG>(P, n0, n1, prop);
     real f0 = t0 - pc0, f1 = t1 - pc1;   // old | new
     real r0 = n0 - cc0, r1 = n1 - cc1;   // new | old
-    real lq = (M::fma(r0, r0, r1 * r1) - M::fma(f0, f0, f1 * f1)) * P.inv4g;  // natural log
-    real lr2 = (plog - clog) + real(1.4426950408889634) * lq;
+    // log2 of the ratio: (log2 p(new) - log2 p(old)) + log2(e) (|new - c_old|^2 - |old - c_new|^2) / (4 gamma)
+    real lr2 = M::fma(M::fma(r0, r0, r1 * r1) - M::fma(f0, f0, f1 * f1), P.inv4g_l2e, plog - clog);
     real ratio = M::exp2(lr2);
-    const mask emitted = L::not_(L::gt(u, M::min(real(1), ratio)));
+    // u < 1, so u > min(1, ratio) <=> u > ratio; a NaN ratio compares false and accepts, like Python's min(1, nan) == 1
+    const mask emitted = L::not_(L::gt(u, ratio));
     t0 = L::select(emitted, n0, t0);
     t1 = L::select(emitted, n1, t1);
     cc0 = L::select(emitted, pc0, cc0);
@@ -523,7 +524,8 @@ __device__ __forceinline__ void hist_lanes(const MixIo& io, real t0, real t1, ty
 // Production loop over steps [kb, ke): Philox noise, registers only.  STATS = accumulate
 // moments (steps past the burn-in), HIST = bin every io.hist_every-th emitted step.
 // Unadjusted samplers use one Philox block per TWO steps (words x,y for even k, z,w for odd
-// k, block counter k >> 1); adjusted samplers one block per step (x,y normals, z uniform).
+// k, block counter k >> 1); adjusted samplers three words per step (normals, normals, uniform) taken consecutively
+// from the blocks 0, 1, 2, ... of the chain: word 3k + i lives in block (3k + i) >> 2, three blocks per four steps.
 template <typename real, int TARGET, int ALG, int NC, bool STATS, bool HIST, bool MIRROR>
 __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC, MIRROR>& ch, const MixP<real>& P,
                                                const MixIo& io, typename Lanes<real>::cid cid,
@@ -547,17 +549,51 @@ __device__ __forceinline__ void run_production(Chain<real, TARGET, ALG, NC, MIRR
   };
   long long k = kb;
   if (ADJ) {
-    while (k < ke) {
-      const int n = (int)((ke - k) < 32 ? (ke - k) : 32);
+    // step k consumes words 3k, 3k + 1 (normals) and 3k + 2 (uniform) of the chain's stream: 3 blocks per 4 steps
+    using blk = decltype(block(0));
+    auto pick = [](const blk& a, const blk& b, int i) {
+      switch (i) {
+        case 0: return a.x;
+        case 1: return a.y;
+        case 2: return a.z;
+        case 3: return a.w;
+        case 4: return b.x;
+        case 5: return b.y;
+        default: return b.z;
+      }
+    };
+    auto one = [&](long long kk) {   // unaligned head / tail steps
+      const long long w0 = 3 * kk;
+      const int o = (int)(w0 & 3);
+      const blk a = block(w0 >> 2), b = block((w0 >> 2) + 1);
+      real x0, x1;
+      M::normals(pick(a, b, o), pick(a, b, o + 1), x0, x1);
+      after(ch.step(P, x0, x1, M::uniform(pick(a, b, o + 2))));
+    };
+    for (; k < ke && (k & 3); ++k) one(k);
+    while (k + 4 <= ke) {
+      const long long groups = (ke - k) >> 2;
+      const int n = (int)(groups < 8 ? groups : 8);
+      const long long b0 = 3 * (k >> 2);
       for (int j = 0; j < n; ++j) {
-        auto r = block(k + j);
         real x0, x1;
-        M::normals(r.x, r.y, x0, x1);
-        after(ch.step(P, x0, x1, M::uniform(r.z)));
+        const blk a = block(b0 + 3 * j);
+        M::normals(a.x, a.y, x0, x1);
+        after(ch.step(P, x0, x1, M::uniform(a.z)));
+        const blk b = block(b0 + 3 * j + 1);
+        M::normals(a.w, b.x, x0, x1);
+        after(ch.step(P, x0, x1, M::uniform(b.y)));
+        const blk c = block(b0 + 3 * j + 2);
+        M::normals(b.z, b.w, x0, x1);
+        after(ch.step(P, x0, x1, M::uniform(c.x)));
+        M::normals(c.y, c.z, x0, x1);
+        after(ch.step(P, x0, x1, M::uniform(c.w)));
       }
       if (STATS) ch.flush();
-      k += n;
+      k += 4 * n;
     }
+    for (; k < ke; ++k) one(k);
+    if (STATS) ch.flush();
     return;
   }
   if ((k & 1) && k < ke) {   // odd start (odd burn-in): second half of block k >> 1
@@ -767,10 +803,14 @@ __global__ void philox_draws_kernel(int adjusted, long long C, long long K, uint
   uint4 rnd = make_uint4(0, 0, 0, 0);
   for (long long k = 0; k < K; ++k) {
     real x0, x1;
-    if (adjusted) {
-      rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)k, LMC_STREAM_STEP | ((uint32_t)(k >> 32) << 8), c_lo, c_hi), rk);
-      M::normals(rnd.x, rnd.y, x0, x1);
-      if (unif != nullptr) unif[c * K + k] = M::uniform(rnd.z);
+    if (adjusted) {   // words 3k, 3k + 1, 3k + 2 of the chain's stream (run_production)
+      const long long w0 = 3 * k, bi = w0 >> 2;
+      const int o = (int)(w0 & 3);
+      const uint4 a = lmc_philox4x32_10_rk(make_uint4((uint32_t)bi, LMC_STREAM_STEP | ((uint32_t)(bi >> 32) << 8), c_lo, c_hi), rk);
+      const uint4 b = lmc_philox4x32_10_rk(make_uint4((uint32_t)(bi + 1), LMC_STREAM_STEP | ((uint32_t)((bi + 1) >> 32) << 8), c_lo, c_hi), rk);
+      const uint32_t wd[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      M::normals(wd[o], wd[o + 1], x0, x1);
+      if (unif != nullptr) unif[c * K + k] = M::uniform(wd[o + 2]);
     } else if ((k & 1) == 0) {
       long long kb = k >> 1;
       rnd = lmc_philox4x32_10_rk(make_uint4((uint32_t)kb, LMC_STREAM_STEP | ((uint32_t)(kb >> 32) << 8), c_lo, c_hi), rk);
@@ -812,6 +852,7 @@ void fill_params(const lmc_mix_target& T, const lmc_mix_step& S, MixP<real>& P) 
   P.gamma = (real)S.gamma;
   P.s2g = (real)sqrt(2 * S.gamma);
   P.inv4g = (real)(1.0 / (4 * S.gamma));
+  P.inv4g_l2e = (real)(1.4426950408889634 / (4 * S.gamma));
   P.m00 = (real)S.M[0]; P.m01 = (real)S.M[1]; P.m10 = (real)S.M[2]; P.m11 = (real)S.M[3];
   P.s00 = (real)S.sqrtM[0]; P.s01 = (real)S.sqrtM[1]; P.s10 = (real)S.sqrtM[2]; P.s11 = (real)S.sqrtM[3];
   P.q00 = (real)S.Q[0]; P.q01 = (real)S.Q[1]; P.q10 = (real)S.Q[2]; P.q11 = (real)S.Q[3];

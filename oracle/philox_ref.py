@@ -51,10 +51,15 @@ def draws(C, K, seed, chain_offset=0, adjusted=False, bits24=False):
     xi = np.empty((C, K, 2))
     un = np.empty((C, K))
     if adjusted:
+        # step k takes words 3k, 3k + 1 (normals) and 3k + 2 (uniform) of the chain's stream of blocks 0, 1, 2, ...
+        # (mix_kernels.cu run_production: three blocks per four steps)
+        nblk = (3 * K + 3) // 4 + 1
+        words = np.concatenate([np.stack(philox4x32_10(np.full(C, b), np.zeros(C), lo, hi, k0, k1), axis=1)
+                                for b in range(nblk)], axis=1)          # (C, 4 nblk)
         for k in range(K):
-            r = philox4x32_10(np.full(C, k), np.zeros(C), lo, hi, k0, k1)
-            xi[:, k, 0], xi[:, k, 1] = _normals(r[0], r[1], bits24)
-            un[:, k] = r[2].astype(np.float64) * 2.0 ** -32 if not bits24 else np.floor(r[2].astype(np.float64) / 256) * 2.0 ** -24
+            a, b, u = words[:, 3 * k], words[:, 3 * k + 1], words[:, 3 * k + 2]
+            xi[:, k, 0], xi[:, k, 1] = _normals(a, b, bits24)
+            un[:, k] = u.astype(np.float64) * 2.0 ** -32 if not bits24 else np.floor(u.astype(np.float64) / 256) * 2.0 ** -24
         return theta0, xi, un
     for kb in range((K + 1) // 2):
         r = philox4x32_10(np.full(C, kb), np.zeros(C), lo, hi, k0, k1)
