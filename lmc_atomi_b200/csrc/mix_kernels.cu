@@ -48,9 +48,12 @@ struct MixP {
   // l1 prior (GAUSS_L1)
   real pr_alpha, pr_thr, pr_mu0, pr_mu1;
   // step
+  real ngs;   // -gamma (Gaussian mixture) or -gamma / lamda (Laplacian): scale from (gp0, gp1) / S to the ULA drift
   real gamma, s2g, inv4g, inv4g_l2e;   // inv4g_l2e = log2(e) / (4 gamma)
   real m00, m01, m10, m11;      // M
   real s00, s01, s10, s11;      // sqrtm(M)
+  real gm00, gm01, gm10, gm11;  // -gamma M            (fp32 production PULA: the step as four FMAs per coordinate)
+  real gs00, gs01, gs10, gs11;  // sqrt(2 gamma) sqrtm(M)
   real q00, q01, q10, q11;      // Q
   real qi00, qi01, qi10, qi11;  // Q^-1
   real eta, inv_eta, pp_thr;    // PPULA dual step, 1/eta, lamda/eta
@@ -81,6 +84,7 @@ struct MixIo {
 template <typename real>
 struct Eval {
   real g0, g1;       // grad U
+  real gp0, gp1, rS; // its pieces: grad U = (gp0, gp1) * rS [* 1/lamda for the Laplacian mixture]
   real logp2;        // log2 of the (smoothed) mixture density
   real h00, h01, h11;  // Hessian of U (only when requested)
 };
@@ -141,6 +145,7 @@ __device__ __forceinline__ void eval_gauss(const MixP<real>& P, real t0, real t1
     sums(amax);
   }
   real rS = M::rcp(S);
+  e.gp0 = gp0; e.gp1 = gp1; e.rS = rS;
   e.g0 = gp0 * rS;
   e.g1 = gp1 * rS;
   e.logp2 = amax + M::log2(S);
@@ -215,6 +220,7 @@ __device__ __forceinline__ void eval_laplace(const MixP<real>& P, real t0, real 
     sums(amax);
   }
   const real rS = M::rcp(S), gS = rS * P.inv_lamda;
+  e.gp0 = gp0; e.gp1 = gp1; e.rS = rS;
   e.g0 = gp0 * gS;
   e.g1 = gp1 * gS;
   e.logp2 = amax + M::log2(S);
@@ -284,11 +290,21 @@ __device__ __forceinline__ void step_unadjusted(const MixP<real>& P, real& t0, r
     t1 = lmc_soft(t1, P.pr_thr);
   }
   eval_target<real, TARGET, NC, AlgTraits<ALG>::hess>(P, t0, t1, e);
-  if (ALG == LMC_ULA || ALG == LMC_PGLD || ALG == LMC_MYULA) {
+  if (ALG == LMC_ULA && !M::is_double) {
+    // float32: -gamma [/ lamda] folded into the normalisation 1 / S, one multiply instead of three
+    const real k = e.rS * P.ngs;
+    t0 = M::fma(P.s2g, x0, M::fma(e.gp0, k, t0));
+    t1 = M::fma(P.s2g, x1, M::fma(e.gp1, k, t1));
+  } else if (ALG == LMC_ULA || ALG == LMC_PGLD || ALG == LMC_MYULA) {
     real c0, c1;
     drift_centre<real, ALG>(P, t0, t1, e, c0, c1);
     t0 = M::fma(P.s2g, x0, c0);
     t1 = M::fma(P.s2g, x1, c1);
+  } else if (ALG == LMC_PULA && !M::is_double) {
+    // theta - gamma M grad U + sqrt(2 gamma) sqrtm(M) xi with the scalars folded into the matrices on the host
+    // (float32 only: float64 keeps the reference's order of operations below)
+    t0 = M::fma(P.gs00, x0, M::fma(P.gs01, x1, M::fma(P.gm00, e.g0, M::fma(P.gm01, e.g1, t0))));
+    t1 = M::fma(P.gs10, x0, M::fma(P.gs11, x1, M::fma(P.gm10, e.g0, M::fma(P.gm11, e.g1, t1))));
   } else if (ALG == LMC_PULA || ALG == LMC_PPULA) {
     real n0 = M::fma(P.m00, e.g0, P.m01 * e.g1), n1 = M::fma(P.m10, e.g0, P.m11 * e.g1);
     real z0 = M::fma(P.s00, x0, P.s01 * x1), z1 = M::fma(P.s10, x0, P.s11 * x1);
@@ -853,8 +869,16 @@ void fill_params(const lmc_mix_target& T, const lmc_mix_step& S, MixP<real>& P) 
   P.s2g = (real)sqrt(2 * S.gamma);
   P.inv4g = (real)(1.0 / (4 * S.gamma));
   P.inv4g_l2e = (real)(1.4426950408889634 / (4 * S.gamma));
+  P.ngs = (real)(T.kind == LMC_TARGET_LAPLACE ? (T.lamda != 0 ? -S.gamma / T.lamda : 0.0) : -S.gamma);
   P.m00 = (real)S.M[0]; P.m01 = (real)S.M[1]; P.m10 = (real)S.M[2]; P.m11 = (real)S.M[3];
   P.s00 = (real)S.sqrtM[0]; P.s01 = (real)S.sqrtM[1]; P.s10 = (real)S.sqrtM[2]; P.s11 = (real)S.sqrtM[3];
+  {
+    const double s2g = sqrt(2.0 * S.gamma);
+    P.gm00 = (real)(-S.gamma * S.M[0]); P.gm01 = (real)(-S.gamma * S.M[1]);
+    P.gm10 = (real)(-S.gamma * S.M[2]); P.gm11 = (real)(-S.gamma * S.M[3]);
+    P.gs00 = (real)(s2g * S.sqrtM[0]); P.gs01 = (real)(s2g * S.sqrtM[1]);
+    P.gs10 = (real)(s2g * S.sqrtM[2]); P.gs11 = (real)(s2g * S.sqrtM[3]);
+  }
   P.q00 = (real)S.Q[0]; P.q01 = (real)S.Q[1]; P.q10 = (real)S.Q[2]; P.q11 = (real)S.Q[3];
   P.qi00 = (real)S.Qinv[0]; P.qi01 = (real)S.Qinv[1]; P.qi10 = (real)S.Qinv[2]; P.qi11 = (real)S.Qinv[3];
   P.eta = (real)S.eta;

@@ -41,6 +41,10 @@ __global__ void __launch_bounds__(256) k(float* out, float s, unsigned u, long l
       if (MODE == 5) { p[i] = fma2(p[i], ps, pc); q[i] = (q[i] ^ u) + (q[i] >> 3); }  // FFMA2 + ALU
       if (MODE == 6) { p[i] = fma2(p[i], ps, pc); q[i] = q[i] * u + 12345u; }         // FFMA2 + IMAD
       if (MODE == 7) { a[i] = fmaf(a[i], s, s); q[i] = q[i] * u + 12345u; }           // FFMA + IMAD
+      if (MODE == 9) a[i] = fminf(fmaxf(a[i], -s), s) + 0.0f * s;        // 2 FMNMX (clamp)
+      if (MODE == 10) { a[i] = fminf(fmaxf(a[i], -s), s); a[i] = fmaf(a[i], s, s); }   // 2 FMNMX + FFMA
+      if (MODE == 11) q[i] = (q[i] & u) ^ (q[i] | 0x5555u);                // LOP3
+      if (MODE == 12) { p[i] = fma2(p[i], ps, pc); a[i] = fminf(fmaxf(a[i], -s), s); }   // FFMA2 + 2 FMNMX
       if (MODE == 8) { unsigned long long w = (unsigned long long)q[i] * 0xD2511F53u; q[i] = (unsigned)(w >> 32) ^ (unsigned)w ^ u; }  // Philox-like
     }
   }
@@ -92,6 +96,10 @@ int main() {
     run<6>("FFMA2 + IMAD", 2, b);
     run<7>("FFMA + IMAD", 2, b);
     run<8>("IMAD.WIDE + 2 LOP3", 3, b);
+    run<9>("2 FMNMX (clamp)", 2, b);
+    run<10>("2 FMNMX + FFMA", 3, b);
+    run<11>("LOP3", 1, b);
+    run<12>("FFMA2 + 2 FMNMX", 3, b);
   }
   return 0;
 }
