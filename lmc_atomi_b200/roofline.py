@@ -71,12 +71,12 @@ def mix_laneops_per_step(target: str, alg: str, t: int = 100) -> float:
 # loop (scripts/sass_loop_census.py -> MIX_CENSUS).  A packed instruction holds the dispatch port for two cycles on
 # B200 (profiles/r02c_ubench_issue.txt: FFMA2 0.5 vs FFMA 1.0 warp-instructions / clock / sub-partition), so the
 # dispatch slots a step needs are instr x (1 + packed share).  Refreshed whenever mix_kernels.cu changes.
-MIX_PROFILE = "profiles/r02i_mix_ncu_full_summary.csv"
-MIX_CENSUS = "profiles/r02i_mix_sass_census.txt"
-MIX_SASS_INSTR_PER_STEP = {"float32": {"ula": 106.4, "mala": 155.3, "pula": 112.6, "mla": 132.4}}
-MIX_PACKED_SHARE = {"float32": {"ula": 0.368, "mala": 0.303, "pula": 0.383, "mla": 0.333}}
-MIX_ISSUE_ACTIVE_PCT = {"ula": 67.2, "mala": 65.4, "pula": 67.9, "mla": 61.6}       # smsp__issue_active, same capture
-MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 150.0e3, "mala": 116.7e3, "pula": 150.0e3, "mla": 153.3e3}   # state is in registers
+MIX_PROFILE = "profiles/r02ac_mix_ncu_full_summary.csv"
+MIX_CENSUS = "profiles/r02ac_mix_sass_census.txt"
+MIX_SASS_INSTR_PER_STEP = {"float32": {"ula": 105.4, "mala": 140.8, "pula": 110.1, "mla": 121.4}}
+MIX_PACKED_SHARE = {"float32": {"ula": 0.361, "mala": 0.330, "pula": 0.373, "mla": 0.388}}
+MIX_ISSUE_ACTIVE_PCT = {"ula": 67.0, "mala": 64.8, "pula": 67.8, "mla": 62.9}       # smsp__issue_active, same capture
+MIX_DRAM_BYTES_PER_LAUNCH = {"ula": 147.7e3, "mala": 152.8e3, "pula": 150.3e3, "mla": 165.6e3}   # state is in registers
 
 
 def mix_roofline(alg: str, chain_steps_per_sec: float, sm_mhz: float, dtype: str = "float32"):
