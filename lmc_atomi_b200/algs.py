@@ -74,17 +74,24 @@ def _engine(proxf, dtype):
     return imaging.DeconvEngine(dims, h, np.asarray(proxf.b, dtype=np.float64), float(proxf.sigma), dtype=dtype)
 
 
+def _lsqr_limit(proxf, count):
+    """``iter_lim`` of the LSQR solve inside ``proxf.prox``: ``niter`` itself, or ``niter(count)`` when it is a callable
+    of the prox call count (already incremented for the call, as pyproximal's ``_increment_count`` does; algs.py:203-207)."""
+    n = proxf.niter
+    return int(n(count)) if callable(n) else int(n)
+
+
 def _moreau_term(proxf, dims):
     """None for pyproximal.L2; the MC-TV / ME-TV term of an L2_ncvx_tv (algs.py:164-170)."""
     if _kind(proxf) != "L2_ncvx_tv":
         return None
     _require(tuple(int(d) for d in proxf.dims) == tuple(dims), "L2_ncvx_tv dims must equal the image dims")
-    _require(isinstance(proxf.niter, int), "callable niter")
     _require(getattr(proxf, "densesolver", None) is None, "dense solvers")
     if proxf.Op2 is not None:
         _require(_is_gradient(proxf.Op2, dims), "Op2 must be pylops.Gradient(dims, kind='forward', edge=False)")
         return imaging.MoreauTerm("mc", proxf.lamda, proxf.gamma, bool(proxf.isotropic))
     _require(bool(proxf.isotropic), "ME-TV with the 1-D TV of algs.py:170")
+    _require(not callable(proxf.niter), "ME-TV with a callable niter (it also sets the inner TV's iteration count)")
     return imaging.MoreauTerm("me", proxf.lamda, proxf.gamma, True, int(proxf.niter), float(proxf.rtol))
 
 
@@ -285,7 +292,8 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
     out = np.empty((niter, P), dtype=np.float64) if rmean is None else None
     outy = np.empty((niter, 2 * P), dtype=np.float64) if returny else None
     need_y = returny or (callback is not None and callbacky)
-    per_iter = callback is not None or show or not constant
+    count0 = int(getattr(proxf, "count", 0))
+    per_iter = callback is not None or show or not constant or callable(proxf.niter)   # niter(count): one launch each
     need_samples = rmean is None or per_iter or device_metrics is not None
     step = 1 if per_iter else _chunk(niter, P, x.element_size(), 2 + (2 if need_y else 0))
     if not philox and not per_iter:
@@ -298,7 +306,7 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
         samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev) if need_samples else None
         ys = torch.empty((1, n, 2, P), dtype=eng.tdt, device=eng.dev) if need_y else None
         keep = eng.ulpda(x, xhat, y, warm, n, float(tau[done]), float(mu[done]), float(theta), float(proxg.sigma),
-                         iso, gfirst, int(proxf.niter), warm_start=warm_on, atol=kw.get("atol", 1e-6),
+                         iso, gfirst, _lsqr_limit(proxf, count0 + done + 1), warm_start=warm_on, atol=kw.get("atol", 1e-6),
                          btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=z, seed=seed, noise=nz,
                          samples=samples, ysamples=ys, iter_offset=done, ncvx=ncvx,
                          mean=None if rmean is None else rmean.t, stat_count0=done)
@@ -394,7 +402,7 @@ class L2_ncvx_tv:
         warm = self._dev(self.x0).clone() if (self.x0 is not None and self.warm) else \
             torch.zeros((1, eng.P), dtype=torch.float64, device=eng.dev)
         kw = self.kwargs_solver
-        out = eng.l2_prox(arg, tau, warm, iter_lim=int(self.niter), atol=kw.get("atol", 1e-6),
+        out = eng.l2_prox(arg, tau, warm, iter_lim=_lsqr_limit(self, self.count), atol=kw.get("atol", 1e-6),
                           btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8))
         out = out.cpu().numpy().reshape(np.shape(x))
         if self.warm:

@@ -188,7 +188,7 @@ class L2(ProxOperator):
         if Op is None or b is None:
             raise NotImplementedError("the CUDA path covers L2 with an operator and data")
         self.b, self.q, self.sigma, self.alpha, self.qgrad = b, q, sigma, alpha, qgrad
-        self.niter, self.x0, self.warm, self.count = int(niter), x0, warm, 0
+        self.niter, self.x0, self.warm, self.count = (niter if callable(niter) else int(niter)), x0, warm, 0
         self.kwargs_solver = {} if kwargs_solver is None else kwargs_solver
         self._eng = None
 
@@ -210,10 +210,12 @@ class L2(ProxOperator):
     def prox(self, x, tau):
         eng = self._engine()
         torch = eng.torch
+        self.count += 1      # pyproximal's _increment_count; a callable niter sees the incremented count
+        lim = int(self.niter(self.count)) if callable(self.niter) else self.niter
         warm = _dev(self.x0, (1, -1)).clone() if (self.x0 is not None and self.warm) else \
             torch.zeros((1, eng.P), dtype=torch.float64, device=eng.dev)
         kw = self.kwargs_solver
-        out = eng.l2_prox(_dev(x, (1, -1)), tau, warm, iter_lim=self.niter, atol=kw.get("atol", 1e-6),
+        out = eng.l2_prox(_dev(x, (1, -1)), tau, warm, iter_lim=lim, atol=kw.get("atol", 1e-6),
                           btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8))
         out = out.cpu().numpy().reshape(np.shape(x))
         if self.warm:

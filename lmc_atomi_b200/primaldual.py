@@ -67,6 +67,7 @@ def AdaptivePrimalDual(proxf, proxg, A, x0, tau, mu, alpha=0.5, eta=0.95, s=1., 
               % (type(proxf), type(proxg), type(A), tau, mu, alpha, eta, s, delta, niter, tol))
         print('   Itn       x[0]          f           g          z^x       J = f + g + z^x')
     iiter = 0
+    count0 = int(getattr(proxf, "count", 0))
     while iiter < niter:
         xold = x.clone()
         # primal step: x - tau (A^T y + z), [L2_ncvx_tv: + tau lamda grad_moreau, algs.py:208-223], LSQR solve
@@ -75,7 +76,7 @@ def AdaptivePrimalDual(proxf, proxg, A, x0, tau, mu, alpha=0.5, eta=0.95, s=1., 
             arg = imaging.moreau_apply(dims, arg, ncvx, tau=tau)
         if not warm_on:
             warm.zero_()
-        x = eng.l2_prox(arg, tau, warm, iter_lim=int(proxf.niter), atol=kw.get("atol", 1e-6),
+        x = eng.l2_prox(arg, tau, warm, iter_lim=algs._lsqr_limit(proxf, count0 + iiter + 1), atol=kw.get("atol", 1e-6),
                         btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8))
         with torch.cuda.device(eng.dev):
             rc = lib.lmc_img_pdhg_dual(dt, dims[0], dims[1], mu, g_sigma, 1 if iso else 0, x.data_ptr(), Ax.data_ptr(),

@@ -283,7 +283,8 @@ class L2(ProxOperator):
         return LinearOperator((n, n), matvec=mv, rmatvec=mv, dtype=np.float64)
 
     def _solve(self, y, tau):
-        out = sp_lsqr(self._op1(tau), y, iter_lim=self.niter, x0=self.x0, **self.kwargs_solver)
+        niter = self.niter if isinstance(self.niter, int) else self.niter(self.count)   # algs.py:203-207
+        out = sp_lsqr(self._op1(tau), y, iter_lim=niter, x0=self.x0, **self.kwargs_solver)
         self.lsqr_itn.append(out[2])
         self.last_istop = out[1]
         return out[0]

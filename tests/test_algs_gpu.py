@@ -107,3 +107,26 @@ def test_unsupported_combination_raises():
         algs.MoreauYosidaUnadjustedLangevin(l2, compat.L1(0.3), pb["x0"], tau=0.1, gamma=0.5, niter=2)
     with pytest.raises(NotImplementedError):
         algs.UnadjustedLangevinPrimalDual(l2, compat.TV(dims), compat.Gradient(dims), pb["x0"], 0.5, 1.0, niter=2)
+
+
+def test_ulpda_callable_niter_follows_the_prox_call_count():
+    """``niter`` as a function of the prox call count (algs.py:203-207, pyproximal.L2): the LSQR iteration limit of
+    sampler iteration n is niter(count0 + n + 1); the wrapper advances one launch per iteration."""
+    from lmc_atomi_b200 import algs
+    dims, N = (40, 36), 7
+    D, compat, pb, H, _ = _setup(dims)
+    sched = lambda count: 2 + count                # 3, 4, 5, ...: below the 10 iterations an unrestricted solve takes here
+    ref = pb["l2"]()
+    ref.niter = sched
+    want = D.UnadjustedLangevinPrimalDual(ref, pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], theta=1.,
+                                          niter=N, seed=4, gfirst=False)
+    assert ref.lsqr_itn == [3, 4, 5, 6, 7, 8, 9]   # the limits bind: the schedule is what is being tested
+    l2 = compat.L2(Op=H, b=pb["y"].ravel(), sigma=1 / 0.75 ** 2, niter=sched, warm=True)
+    got = algs.UnadjustedLangevinPrimalDual(l2, compat.L21(ndim=2, sigma=0.3), compat.Gradient(dims), pb["x0"],
+                                            tau=pb["tau0"], mu=pb["mu0"], theta=1., niter=N, seed=4, gfirst=False)
+    assert rel(got, want) < 1e-10
+    assert l2.count == N
+    # the operator's own prox honours the schedule too (count keeps running)
+    x = np.random.default_rng(0).normal(100, 20, dims[0] * dims[1])
+    a, b = ref.prox(x.copy(), 0.3), l2.prox(x.copy(), 0.3)
+    assert ref.lsqr_itn[-1] <= sched(N + 1) and ref.count == l2.count == N + 1 and rel(b, a) < 1e-10
