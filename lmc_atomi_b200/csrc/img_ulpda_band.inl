@@ -102,7 +102,6 @@ __device__ void band_primal_init(const UlpdaArgs<real>& A, BandSched& sched, lon
     };
     BandPf<real, W, 2, UB_PFD> pf;
     band_prefetch<real, RB, W, 2, UB_PFD>(g, i0, W * threadIdx.x, pf, pre);
-    __syncthreads();
     if (A.warm_on) {
       band_stage(sched, X, pitch, zw, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     } else {
@@ -204,7 +203,6 @@ __device__ void band_ka(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     };
     BandPf<real, W, 3, UB_PFD> pf;
     band_prefetch<real, RB, W, 3, UB_PFD>(g, i0, W * threadIdx.x, pf, pre);
-    __syncthreads();
     band_stage(sched, X, pitch, A.v + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
@@ -272,7 +270,6 @@ __device__ void band_kb(const UlpdaArgs<real>& A, BandSched& sched, long long c_
     auto pre = [&](int i, int c, Pack<real, W> (&v)[1]) { v[0] = ldp<real, W>(vC + i * g.nx + c); };
     BandPf<real, W, 1, UB_PFD> pf;
     band_prefetch<real, RB, W, 1, UB_PFD>(g, i0, W * threadIdx.x, pf, pre);
-    __syncthreads();
     band_stage(sched, X, pitch, A.u + chain * g.P, g.ny, g.nx, i0 - E, Band<real, NT, RB>::XROWS);
     band_forward<real, NT, RB, W>(g, X, T, pitch, i0, wx, wy);
     __syncthreads();
