@@ -210,8 +210,10 @@ typedef struct lmc_img_io {
   /* Non-convex data terms (algs.L2_ncvx_tv, algs.py:22-291): the Moreau-envelope term is evaluated by the
    * unit entry points below between launches, so both need N == 1 (and gfirst == 0 for ULPDA).
    * Streaming / band kernels only (not lmc_img_myula_run_onchip). */
-  const void* d_fgrad_extra; /* (C,P) MYULA: grad f(x) = sigma H^T(Hx - b) + fgrad_scale * this  (algs.py:283-291) */
-  double fgrad_scale;        /* -lamda */
+  const void* d_fgrad_extra; /* (C,P) MYULA: grad f(x) = sigma H^T(Hx - b) + fgrad_scale * this; read every iteration of the
+                                launch: a per-iteration term (the Moreau gradient, algs.py:283-291, fgrad_scale = -lamda)
+                                needs N == 1, a constant one (alpha q of L2 / L2_ncvx_tv, algs.py:288-289) any N */
+  double fgrad_scale;
   const void* d_prox_arg;    /* (C,P) ULPDA: replaces x - tau (G^T y + z) as the argument of the L2 prox (algs.py:224-256) */
   const lmc_img_ncvx* ncvx;  /* HOST pointer or NULL: non-convex term evaluated in-kernel, any N (streaming / band kernels
                                 of both samplers; ULPDA needs lmc_img_ulpda_workspace_bytes_ncvx); excludes

@@ -60,8 +60,6 @@ def _blur_of(proxf):
     _require(Op is not None and hasattr(Op, "h") and hasattr(Op, "dims"),
              "proxf.Op must be a Convolve2D-like operator exposing .h and .dims")
     _require(getattr(proxf, "b", None) is not None, "proxf must carry data b")
-    _require(getattr(proxf, "q", None) is None and getattr(proxf, "alpha", 1.0) == 1.0,
-             "L2 with q/alpha terms")
     dims = tuple(int(d) for d in Op.dims)
     _require(len(dims) == 2, "2-D images")
     return dims, np.asarray(Op.h, dtype=np.float64)
@@ -72,6 +70,16 @@ def _engine(proxf, dtype):
              f"proxf of type {_kind(proxf)}; supported: pyproximal.L2, algs.L2_ncvx_tv")
     dims, h = _blur_of(proxf)
     return imaging.DeconvEngine(dims, h, np.asarray(proxf.b, dtype=np.float64), float(proxf.sigma), dtype=dtype)
+
+
+def _linear_term(proxf, P):
+    """alpha * q of pyproximal.L2 / algs.L2_ncvx_tv (algs.py:186-187, 226-227, 288-289) as a float64 (P,) array, or None."""
+    q = getattr(proxf, "q", None)
+    if q is None:
+        return None
+    q = np.asarray(q, dtype=np.float64).ravel()
+    _require(q.size == P, "q must have one entry per pixel")
+    return float(getattr(proxf, "alpha", 1.0)) * q
 
 
 def _lsqr_limit(proxf, count):
@@ -192,6 +200,10 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
     _require(tuple(int(d) for d in proxg.dims) == eng.dims, "TV dims must equal the image dims")
     x0 = np.asarray(x0, dtype=np.float64)
     P = eng.P
+    # alpha q enters grad f when qgrad (algs.py:288-289): a constant extra gradient term of the kernels
+    aq = _linear_term(proxf, P) if getattr(proxf, "qgrad", True) else None
+    _require(aq is None or ncvx is None, "MYULA with both a non-convex term and a q term")
+    fextra = None if aq is None else eng._buf(aq, 1)
     if show:   # banner / header / line formats verbatim from algs.py:545-560, 576-583 (output compatibility)
         tstart = time.time()
         print('Moreau--Yosida Unadjusted Langevin\n'
@@ -217,7 +229,8 @@ def MoreauYosidaUnadjustedLangevin(proxf, proxg, x0, tau=None, gamma=.1, epsg=1.
         samples = torch.empty((1, n, P), dtype=eng.tdt, device=eng.dev) if need_samples else None
         keep = eng.myula(x, n, tau, gamma, float(proxg.sigma), int(proxg.niter), float(proxg.rtol),
                          epsg=float(epsg), seed=seed, noise=nz, samples=samples, iter_offset=done, ncvx=ncvx,
-                         mean=None if rmean is None else rmean.t, stat_count0=done)
+                         mean=None if rmean is None else rmean.t, stat_count0=done,
+                         fgrad_extra=fextra, fgrad_scale=1.0 if fextra is not None else 0.0)
         if device_metrics is not None:
             device_metrics._extend(eng.sample_metrics(samples[0], device_metrics.xtrue, float(proxg.sigma), True))
         if out is not None:
@@ -267,6 +280,11 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
     _require(getattr(proxg, "g", None) is None, "L1 with a shift vector")
     _require(_is_gradient(A, eng.dims), "A must be pylops.Gradient(dims, kind='forward', edge=False)")
     x0 = np.asarray(x0, dtype=np.float64)
+    # y = x + tau OpTb - tau alpha q (algs.py:226-227) with x = x - tau (A^T y + z): alpha q adds to z.  With a non-convex
+    # term the Moreau pre-step sits between the two (algs.py:208-223), so the fold would move its evaluation point.
+    aq = _linear_term(proxf, P)
+    _require(aq is None or ncvx is None, "ULPDA with both a non-convex term and a q term")
+    zk = z if aq is None else (aq if z is None else np.asarray(z, dtype=np.float64).ravel() + aq)
     # algs.py:401-408: scalars become constant arrays
     fixedtau, fixedmu = isinstance(tau, (int, float)), isinstance(mu, (int, float))
     tau = tau * np.ones(niter, dtype=x0.dtype) if fixedtau else np.asarray(tau, dtype=np.float64)
@@ -307,7 +325,7 @@ def UnadjustedLangevinPrimalDual(proxf, proxg, A, x0, tau, mu, y0=None, z=None, 
         ys = torch.empty((1, n, 2, P), dtype=eng.tdt, device=eng.dev) if need_y else None
         keep = eng.ulpda(x, xhat, y, warm, n, float(tau[done]), float(mu[done]), float(theta), float(proxg.sigma),
                          iso, gfirst, _lsqr_limit(proxf, count0 + done + 1), warm_start=warm_on, atol=kw.get("atol", 1e-6),
-                         btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=z, seed=seed, noise=nz,
+                         btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8), z=zk, seed=seed, noise=nz,
                          samples=samples, ysamples=ys, iter_offset=done, ncvx=ncvx,
                          mean=None if rmean is None else rmean.t, stat_count0=done)
         if device_metrics is not None:
@@ -388,6 +406,9 @@ class L2_ncvx_tv:
         xd = self._dev(x)
         r = imaging.blur(eng.spec, xd) - eng.b
         g = (self.sigma * imaging.blur(eng.spec, r, adjoint=True)).cpu().numpy().reshape(np.shape(x))
+        aq = _linear_term(self, eng.P)
+        if aq is not None and self.qgrad:      # algs.py:288-289
+            g = g + aq.reshape(np.shape(x))
         return g - self.lamda * self.grad_moreau(x)
 
     def prox(self, x, tau):
@@ -399,6 +420,9 @@ class L2_ncvx_tv:
         arg = imaging.moreau_apply(eng.dims, self._dev(x), term, tau=float(tau))
         if isinstance(x, np.ndarray) and x.dtype == np.float64:
             x[...] = arg.cpu().numpy().reshape(x.shape)
+        aq = _linear_term(self, eng.P)
+        if aq is not None:      # y = x + tau OpTb - tau alpha q (algs.py:226-227)
+            arg = arg - float(tau) * self._dev(aq)
         warm = self._dev(self.x0).clone() if (self.x0 is not None and self.warm) else \
             torch.zeros((1, eng.P), dtype=torch.float64, device=eng.dev)
         kw = self.kwargs_solver
@@ -426,4 +450,7 @@ class L2_ncvx_tv:
             mp = imaging.tv_prox(eng.dims, xd, g, int(self.niter), float(self.rtol))
             dg = imaging.grad(eng.dims, mp)[0]
             env = float((dg.pow(2).sum(dim=0).sqrt().sum() + (xd - mp).pow(2).sum() / (2 * g)).item())
+        aq = _linear_term(self, eng.P)
+        if aq is not None:      # algs.py:186-187
+            f += float(np.dot(aq, np.asarray(x, dtype=np.float64).ravel()))
         return f - self.lamda * env

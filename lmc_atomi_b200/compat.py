@@ -183,8 +183,8 @@ class L2(ProxOperator):
     def __init__(self, Op=None, b=None, q=None, sigma=1.0, alpha=1.0, qgrad=True, niter=10, x0=None,
                  warm=True, densesolver=None, kwargs_solver=None):
         super().__init__(Op, True)
-        if q is not None or alpha != 1.0 or densesolver is not None:
-            raise NotImplementedError("L2 with q / alpha / densesolver is not on the reference's path")
+        if densesolver is not None:
+            raise NotImplementedError("L2 with a dense solver (explicit operators) has no CUDA path")
         if Op is None or b is None:
             raise NotImplementedError("the CUDA path covers L2 with an operator and data")
         self.b, self.q, self.sigma, self.alpha, self.qgrad = b, q, sigma, alpha, qgrad
@@ -200,12 +200,18 @@ class L2(ProxOperator):
     def __call__(self, x):
         eng = self._engine()
         r = imaging.blur(eng.spec, _dev(x, (1, -1))) - eng.b
-        return float(self.sigma / 2.0 * r.pow(2).sum().item())
+        f = float(self.sigma / 2.0 * r.pow(2).sum().item())
+        if self.q is not None:      # pyproximal.L2: + alpha q^T x
+            f += float(self.alpha * np.dot(np.asarray(self.q, dtype=np.float64).ravel(), np.asarray(x, dtype=np.float64).ravel()))
+        return f
 
     def grad(self, x):
         eng = self._engine()
         r = imaging.blur(eng.spec, _dev(x, (1, -1))) - eng.b
-        return (self.sigma * imaging.blur(eng.spec, r, adjoint=True)).cpu().numpy().reshape(np.shape(x))
+        g = (self.sigma * imaging.blur(eng.spec, r, adjoint=True)).cpu().numpy().reshape(np.shape(x))
+        if self.q is not None and self.qgrad:
+            g = g + self.alpha * np.asarray(self.q, dtype=np.float64).reshape(np.shape(x))
+        return g
 
     def prox(self, x, tau):
         eng = self._engine()
@@ -215,7 +221,10 @@ class L2(ProxOperator):
         warm = _dev(self.x0, (1, -1)).clone() if (self.x0 is not None and self.warm) else \
             torch.zeros((1, eng.P), dtype=torch.float64, device=eng.dev)
         kw = self.kwargs_solver
-        out = eng.l2_prox(_dev(x, (1, -1)), tau, warm, iter_lim=lim, atol=kw.get("atol", 1e-6),
+        xin = _dev(x, (1, -1))
+        if self.q is not None:      # y = x + tau OpTb - tau alpha q
+            xin = xin - float(tau) * self.alpha * _dev(np.asarray(self.q, dtype=np.float64), (1, -1))
+        out = eng.l2_prox(xin, tau, warm, iter_lim=lim, atol=kw.get("atol", 1e-6),
                           btol=kw.get("btol", 1e-6), conlim=kw.get("conlim", 1e8))
         out = out.cpu().numpy().reshape(np.shape(x))
         if self.warm:

@@ -172,7 +172,6 @@ extern "C" int lmc_img_myula_run(const lmc_img_problem* pb, const lmc_img_myula_
   LMC_REQUIRE(io->d_x != nullptr && pb->d_b != nullptr, "lmc_img_myula_run: d_x and d_b are required");
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_myula_run: b_chain_stride must be 0 or ny*nx");
-  LMC_REQUIRE(io->d_fgrad_extra == nullptr || N == 1, "lmc_img_myula_run: d_fgrad_extra needs N == 1");
   LMC_REQUIRE(io->ncvx == nullptr || io->ncvx->kind == 0 || io->d_fgrad_extra == nullptr,
               "lmc_img_myula_run: ncvx and d_fgrad_extra are two ways to pass the same term");
   LMC_REQUIRE(io->ncvx == nullptr || (io->ncvx->kind >= 0 && io->ncvx->kind <= 2 && (io->ncvx->kind == 0 ||
@@ -207,7 +206,6 @@ extern "C" int lmc_img_myula_run_band(const lmc_img_problem* pb, const lmc_img_m
   LMC_REQUIRE(io->d_x != nullptr && pb->d_b != nullptr, "lmc_img_myula_run_band: d_x and d_b are required");
   LMC_REQUIRE(pb->b_chain_stride == 0 || pb->b_chain_stride == (int64_t)pb->ny * pb->nx,
               "lmc_img_myula_run_band: b_chain_stride must be 0 or ny*nx");
-  LMC_REQUIRE(io->d_fgrad_extra == nullptr || N == 1, "lmc_img_myula_run_band: d_fgrad_extra needs N == 1");
   LMC_REQUIRE(io->ncvx == nullptr || io->ncvx->kind == 0 || io->d_fgrad_extra == nullptr,
               "lmc_img_myula_run_band: ncvx and d_fgrad_extra are two ways to pass the same term");
   LMC_REQUIRE(io->ncvx == nullptr || (io->ncvx->kind >= 0 && io->ncvx->kind <= 2 && (io->ncvx->kind == 0 ||

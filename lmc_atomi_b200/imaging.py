@@ -342,8 +342,11 @@ class DeconvEngine:
 
     def myula(self, x, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, epsg=1.0, seed=0, chain_offset=0,
               noise=None, samples=None, mean=None, m2=None, burnin=0, stat_count0=0, iter_offset=0,
-              engine="auto", ncvx=None):
+              engine="auto", ncvx=None, fgrad_extra=None, fgrad_scale=0.0):
         """Advances the (C,P) device tensor ``x`` in place by N MYULA iterations (algs.py:564-583).
+
+        ``fgrad_extra`` / ``fgrad_scale``: a constant (C,P) term added to grad f in every iteration, scaled
+        (alpha q of pyproximal.L2 / L2_ncvx_tv, algs.py:288-289); band / tile kernels, not combined with ``ncvx``.
 
         ``ncvx``: a MoreauTerm makes the data term the reference's L2_ncvx_tv (MC-TV / ME-TV): the band / tile
         kernels evaluate grad_moreau(x) in-kernel every iteration (MC-TV: a 7-point stencil in the gradient phase;
@@ -352,7 +355,8 @@ class DeconvEngine:
         if ncvx is not None and engine == "onchip":
             raise NotImplementedError("the on-chip MYULA kernel has no non-convex data term; use engine='auto'")
         return self._myula_launch(x, N, tau, gamma, tv_sigma, tv_niter, tv_rtol, epsg, seed, chain_offset, noise,
-                                  samples, mean, m2, burnin, stat_count0, iter_offset, engine, ncvx=ncvx)
+                                  samples, mean, m2, burnin, stat_count0, iter_offset, engine, ncvx=ncvx,
+                                  fgrad_extra=fgrad_extra, fgrad_scale=fgrad_scale)
 
     def _myula_launch(self, x, N, tau, gamma, tv_sigma, tv_niter=10, tv_rtol=1e-4, epsg=1.0, seed=0, chain_offset=0,
                       noise=None, samples=None, mean=None, m2=None, burnin=0, stat_count0=0, iter_offset=0,

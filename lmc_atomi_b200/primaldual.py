@@ -68,12 +68,16 @@ def AdaptivePrimalDual(proxf, proxg, A, x0, tau, mu, alpha=0.5, eta=0.95, s=1., 
         print('   Itn       x[0]          f           g          z^x       J = f + g + z^x')
     iiter = 0
     count0 = int(getattr(proxf, "count", 0))
+    aq = algs._linear_term(proxf, P)
+    aq = None if aq is None else eng._buf(aq, 1)
     while iiter < niter:
         xold = x.clone()
         # primal step: x - tau (A^T y + z), [L2_ncvx_tv: + tau lamda grad_moreau, algs.py:208-223], LSQR solve
         arg = imaging.pd_arg(dims, x, y, tau, zt)
         if ncvx is not None:
             arg = imaging.moreau_apply(dims, arg, ncvx, tau=tau)
+        if aq is not None:      # y = x + tau OpTb - tau alpha q (algs.py:226-227), after the Moreau pre-step
+            arg = arg - tau * aq
         if not warm_on:
             warm.zero_()
         x = eng.l2_prox(arg, tau, warm, iter_lim=algs._lsqr_limit(proxf, count0 + iiter + 1), atol=kw.get("atol", 1e-6),

@@ -262,8 +262,10 @@ class L2(ProxOperator):
     """``pyproximal.L2(Op, b, sigma, niter, warm=True)`` (prox_lmc_deconv.py:101-103;
     structure mirrored in the reference's own copy algs.py:158-162,224-256,283-284)."""
 
-    def __init__(self, Op=None, b=None, sigma=1., niter=10, x0=None, warm=True, kwargs_solver=None):
+    def __init__(self, Op=None, b=None, sigma=1., niter=10, x0=None, warm=True, kwargs_solver=None, q=None, alpha=1.,
+                 qgrad=True):
         self.Op, self.b, self.sigma, self.niter = Op, b, sigma, niter
+        self.q, self.alpha, self.qgrad = q, alpha, qgrad      # alpha q^T x (algs.py:186-187, 226-227, 288-289)
         self.x0, self.warm = x0, warm
         self.count = 0
         self.kwargs_solver = {} if kwargs_solver is None else kwargs_solver
@@ -271,10 +273,16 @@ class L2(ProxOperator):
         self.lsqr_itn = []       # LSQR iterations per prox call (roofline accounting)
 
     def __call__(self, x):
-        return (self.sigma / 2.) * (np.linalg.norm(self.Op.matvec(x) - self.b) ** 2)
+        f = (self.sigma / 2.) * (np.linalg.norm(self.Op.matvec(x) - self.b) ** 2)
+        if self.q is not None:
+            f += self.alpha * np.dot(self.q, x)
+        return f
 
     def grad(self, x):
-        return self.sigma * self.Op.rmatvec(self.Op.matvec(x) - self.b)
+        g = self.sigma * self.Op.rmatvec(self.Op.matvec(x) - self.b)
+        if self.q is not None and self.qgrad:
+            g += self.alpha * self.q
+        return g
 
     def _op1(self, tau):
         c = float(tau * self.sigma)
@@ -292,6 +300,8 @@ class L2(ProxOperator):
     def prox(self, x, tau):
         self.count += 1
         y = x + tau * self.OpTb
+        if self.q is not None:
+            y -= tau * self.alpha * self.q
         x = self._solve(y, tau)
         if self.warm:
             self.x0 = x
@@ -304,8 +314,8 @@ class L2_ncvx_tv(L2):
     isotropic, inner TV(dims, 1., niter, rtol))."""
 
     def __init__(self, dims, Op=None, Op2=None, b=None, sigma=1., lamda=1., gamma=.5,
-                 isotropic=False, niter=10, rtol=1e-4, x0=None, warm=True):
-        super().__init__(Op=Op, b=b, sigma=sigma, niter=niter, x0=x0, warm=warm)
+                 isotropic=False, niter=10, rtol=1e-4, x0=None, warm=True, q=None, alpha=1., qgrad=True):
+        super().__init__(Op=Op, b=b, sigma=sigma, niter=niter, x0=x0, warm=warm, q=q, alpha=alpha, qgrad=qgrad)
         self.dims, self.ndim = tuple(dims), len(dims)
         self.Op2, self.lamda, self.gamma, self.isotropic, self.rtol = Op2, lamda, gamma, isotropic, rtol
         if Op2 is not None:
@@ -335,11 +345,15 @@ class L2_ncvx_tv(L2):
         mp = self.g_gamma.prox(Op2x, self.gamma)
         env = self.g_gamma(mp) + np.linalg.norm(Op2x - mp) ** 2 / (2 * self.gamma)
         f = (self.sigma / 2.) * (np.linalg.norm(self.Op.matvec(x) - self.b) ** 2)
+        if self.q is not None:
+            f += self.alpha * np.dot(self.q, x)
         return f - self.lamda * env
 
     def grad(self, x):
         """algs.py:270-291."""
         g = self.sigma * self.Op.rmatvec(self.Op.matvec(x) - self.b)
+        if self.q is not None and self.qgrad:
+            g += self.alpha * self.q
         return g - self.lamda * self.grad_moreau(x)
 
     def prox(self, x, tau):
@@ -347,6 +361,8 @@ class L2_ncvx_tv(L2):
         self.count += 1
         x += tau * self.lamda * self.grad_moreau(x)
         y = x + tau * self.OpTb
+        if self.q is not None:
+            y -= tau * self.alpha * self.q
         x = self._solve(y, tau)
         if self.warm:
             self.x0 = x

@@ -130,3 +130,44 @@ def test_ulpda_callable_niter_follows_the_prox_call_count():
     x = np.random.default_rng(0).normal(100, 20, dims[0] * dims[1])
     a, b = ref.prox(x.copy(), 0.3), l2.prox(x.copy(), 0.3)
     assert ref.lsqr_itn[-1] <= sched(N + 1) and ref.count == l2.count == N + 1 and rel(b, a) < 1e-10
+
+
+def test_linear_term_q_alpha_qgrad():
+    """alpha q^T x of pyproximal.L2 / algs.L2_ncvx_tv (algs.py:186-187, 226-227, 288-289): unit operators, both samplers
+    and the MAP loop against the oracle."""
+    from lmc_atomi_b200 import algs, primaldual
+    dims, N = (40, 36), 5
+    D, compat, pb, H, _ = _setup(dims)
+    P = dims[0] * dims[1]
+    rng = np.random.default_rng(3)
+    q, alpha = rng.normal(0, 0.05, P), 0.7
+    y, sig = pb["y"].ravel(), 1 / 0.75 ** 2
+    ref = lambda **kw: D.L2(Op=pb["H"], b=y, sigma=sig, niter=50, warm=True, q=q, alpha=alpha, **kw)
+    mine = lambda **kw: compat.L2(Op=H, b=y, sigma=sig, niter=50, warm=True, q=q, alpha=alpha, **kw)
+    x = rng.normal(100, 20, P)
+    a, b = ref(), mine()
+    assert abs(b(x) - a(x)) < 1e-9 * abs(a(x)) and rel(b.grad(x), a.grad(x)) < 1e-12
+    assert rel(mine(qgrad=False).grad(x), ref(qgrad=False).grad(x)) < 1e-12
+    assert rel(b.prox(x.copy(), 0.3), a.prox(x.copy(), 0.3)) < 1e-10
+    # ULPDA: alpha q folds into the linear term z
+    z = rng.normal(0, 0.1, P)
+    want = D.UnadjustedLangevinPrimalDual(ref(), pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"], z=z,
+                                          theta=1., niter=N, seed=6, gfirst=False)
+    got = algs.UnadjustedLangevinPrimalDual(mine(), compat.L21(ndim=2, sigma=0.3), compat.Gradient(dims), pb["x0"],
+                                            tau=pb["tau0"], mu=pb["mu0"], z=z, theta=1., niter=N, seed=6, gfirst=False)
+    assert rel(got, want) < 1e-10
+    # MYULA: alpha q is a constant extra gradient term (dropped when qgrad is False)
+    for qgrad in (True, False):
+        want = D.MoreauYosidaUnadjustedLangevin(ref(qgrad=qgrad), pb["tv"](), pb["x0"], tau=pb["tau_myula"],
+                                                gamma=pb["gamma_myula"], niter=N, seed=6)
+        got = algs.MoreauYosidaUnadjustedLangevin(mine(qgrad=qgrad), compat.TV(dims, sigma=0.3, niter=10, rtol=1e-4),
+                                                  pb["x0"], tau=pb["tau_myula"], gamma=pb["gamma_myula"], niter=N, seed=6)
+        assert rel(got, want) < 1e-10
+    # MAP loop with the non-convex MC-TV term: q enters after the Moreau pre-step
+    mk = dict(dims=dims, b=y, sigma=sig, lamda=0.3, gamma=15.0, isotropic=True, niter=50, warm=True, q=q, alpha=alpha)
+    want, _ = D.AdaptivePrimalDual(D.L2_ncvx_tv(Op=pb["H"], Op2=pb["Gop"], **mk), pb["l1iso"](), pb["Gop"], pb["x0"],
+                                   pb["tau0"], pb["mu0"], niter=N)
+    got, _ = primaldual.AdaptivePrimalDual(algs.L2_ncvx_tv(Op=H, Op2=compat.Gradient(dims), **mk),
+                                           compat.L21(ndim=2, sigma=0.3), compat.Gradient(dims), pb["x0"],
+                                           pb["tau0"], pb["mu0"], niter=N)
+    assert rel(got, want) < 1e-9
