@@ -112,3 +112,33 @@ def test_myula_onchip_256_benchmark_shape(torch):
         out[engine] = (x.cpu().numpy(), mean.cpu().numpy())
     for a, b in zip(out["onchip"], out["band"]):
         assert rel(a, b) < 1e-5
+
+
+@pytest.mark.parametrize("sampler", ["myula", "ulpda"])
+def test_band_wide_rows_two_column_groups(torch, sampler):
+    """A 24 x 776 fp32 image: rows wider than 2 x 256 threads (a second, partial column group per thread in every pass),
+    one CTA per SM (139 KB of shared memory), rows staged by 3 KB bulk copies -- against the oracle for a few iterations."""
+    from lmc_atomi_b200 import imaging as I
+    from oracle import deconv_ref as D
+    dims, N = (24, 776), 3
+    pb = D.build_problem(D.synthetic_image(*dims), kernel=5)
+    P = dims[0] * dims[1]
+    noise = D.image_noise(0, N, P)
+    eng = I.DeconvEngine(dims, pb["H"].h, pb["y"].ravel(), 1 / 0.75 ** 2, dtype="float32")
+    z = lambda *s: torch.zeros(s, dtype=eng.tdt, device="cuda")
+    samples = z(1, N, P)
+    if sampler == "myula":
+        assert eng.myula_band_supported()
+        want = D.MoreauYosidaUnadjustedLangevin(pb["l2"](), pb["tv"](), pb["x0"], tau=pb["tau_myula"],
+                                                gamma=pb["gamma_myula"], niter=N, noise=noise)
+        eng.myula(z(1, P), N, pb["tau_myula"], pb["gamma_myula"], 0.3, 10, 1e-4, noise=noise[None], samples=samples,
+                  engine="band")
+    else:
+        assert eng.band_supported()
+        want = D.UnadjustedLangevinPrimalDual(pb["l2"](), pb["l1iso"](), pb["Gop"], pb["x0"], pb["tau0"], pb["mu0"],
+                                              theta=1., niter=N, gfirst=False, noise=noise)
+        eng.ulpda(z(1, P), z(1, P), z(1, 2, P), z(1, P), N, pb["tau0"], pb["mu0"], 1.0, 0.3, True, False, 50,
+                  noise=noise[None], samples=samples, engine="band")
+    got = samples.double().cpu().numpy()[0]
+    errs = [rel(got[n], want[n]) for n in range(N)]
+    assert max(errs) < 2e-5, errs
