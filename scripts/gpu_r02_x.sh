@@ -1,7 +1,7 @@
 #!/bin/bash
 # register/shuffle TV sweep of the MYULA band kernel: parity + rate
-O=gpurun_out/r02y; mkdir -p $O
-timeout 1500 python -m pytest tests -m gpu -q -x -k "img or band or ncvx or chunked or bench_shapes" > $O/tests.log 2>&1; echo "rc=$?" >> $O/tests.log
+O=gpurun_out/r02al; mkdir -p $O
+timeout 1500 python -m pytest tests -m gpu -q -x -k "img or band or ncvx or chunked or bench_shapes or pinned or algs" > $O/tests.log 2>&1; echo "rc=$?" >> $O/tests.log
 tail -n 6 $O/tests.log
 cat > /tmp/ab.py <<'PY'
 import torch, sys
